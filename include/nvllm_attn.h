@@ -1,0 +1,218 @@
+/*
+ * nvllm_attn.h — C ABI of the B200 (sm_100a) paged-attention hot path.
+ *
+ * This is the drop-in boundary for nano-vllm's `Attention.forward(q, k, v)` /
+ * `Context` contract.  Every entry point takes plain device pointers, sizes,
+ * strides (in ELEMENTS unless the name ends in _bytes) and a CUDA stream
+ * handle (cudaStream_t passed as void*), and returns an int status
+ * (NVLLM_OK == 0).  No torch types, no exceptions, no allocation per call:
+ * the caller owns every buffer including the output and the split-KV
+ * workspace, so every call is CUDA-graph capturable.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   nvllm_store_kvcache     <- nanovllm/layers/attention.py:19-55
+ *                              (store_kvcache_kernel + store_kvcache)
+ *   nvllm_paged_decode      <- nanovllm/layers/attention.py:97-101
+ *                              (flash_attn_with_kvcache(q, k_cache, v_cache,
+ *                               cache_seqlens, block_table, softmax_scale))
+ *                              semantics: nanovllm/layers/attention_sdpa.py:122-182
+ *   nvllm_varlen_prefill    <- nanovllm/layers/attention.py:89-96
+ *                              (flash_attn_varlen_func(..., causal=True,
+ *                               block_table=...)); no-prefix semantics:
+ *                              nanovllm/layers/attention_sdpa.py:65-119
+ *   nvllm_prepare_decode / nvllm_prepare_prefill_slots
+ *                           <- nanovllm/engine/model_runner.py:244-269 and
+ *                              :212-221 (index math of the runner glue)
+ *
+ * All tensors are bf16 (2-byte elements) unless stated; index tensors are
+ * int32 exactly as the reference's Context carries them
+ * (nanovllm/utils/context.py:5-14).
+ */
+#ifndef NVLLM_ATTN_H_
+#define NVLLM_ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NVLLM_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define NVLLM_API __attribute__((visibility("default")))
+#else
+#define NVLLM_API
+#endif
+
+enum nvllm_status {
+  NVLLM_OK = 0,
+  NVLLM_ERR_BAD_ARG = 1,      /* null pointer, negative size, bad stride      */
+  NVLLM_ERR_UNSUPPORTED = 2,  /* shape the kernels are not built for          */
+  NVLLM_ERR_ALIGNMENT = 3,    /* pointer/stride not 16-byte aligned           */
+  NVLLM_ERR_CUDA = 4,         /* launch failed; see nvllm_last_cuda_error()   */
+  NVLLM_ERR_WORKSPACE = 5     /* workspace missing or too small               */
+};
+
+/* ABI version of the loaded library (== NVLLM_ABI_VERSION of its build). */
+NVLLM_API int nvllm_abi_version(void);
+
+/* Static string for a status code (never NULL). */
+NVLLM_API const char* nvllm_status_string(int status);
+
+/* cudaError_t of the last failed launch seen by this library (0 if none). */
+NVLLM_API int nvllm_last_cuda_error(void);
+
+/* Number of kernel launches this library has issued since load (or since the
+ * last nvllm_reset_launch_count).  bench.py reports it as `gpu_launches`. */
+NVLLM_API int64_t nvllm_launch_count(void);
+NVLLM_API void nvllm_reset_launch_count(void);
+
+/* ------------------------------------------------------------------------
+ * (1) store_kvcache — slot-mapping scatter into the paged K/V cache.
+ *     reference: nanovllm/layers/attention.py:19-55
+ *
+ *   for i in [0, n_tokens):  s = slot_mapping[i]
+ *     k_cache[s * row_elems + j] = key  [i * key_row_stride   + j]
+ *     v_cache[s * row_elems + j] = value[i * value_row_stride + j]   j < row_elems
+ *   row_elems = num_kv_heads * head_dim.
+ *
+ *   s == -1 (any negative slot) is skipped: superset of the flash-backend
+ *   copy (no guard) and the triton-backend copy (guard,
+ *   attention_triton.py:30-31).  Slots are honoured literally otherwise,
+ *   including duplicated slot 0 of zero-padded CUDA-graph rows
+ *   (model_runner.py:291-293).  Offsets are 64-bit.
+ *
+ *   elem_bytes is 2 (bf16/fp16); row_elems*elem_bytes, both row strides in
+ *   bytes and all four base pointers must be multiples of 16 (16-byte vector
+ *   loads/stores), else NVLLM_ERR_ALIGNMENT.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_store_kvcache(const void* key, int64_t key_row_stride,
+                        const void* value, int64_t value_row_stride,
+                        void* k_cache, void* v_cache,
+                        const int32_t* slot_mapping,
+                        int32_t n_tokens, int32_t num_kv_heads,
+                        int32_t head_dim, int32_t elem_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * (2) paged GQA decode (one query token per sequence).
+ *     reference: nanovllm/layers/attention.py:97-101
+ *
+ *   out[b, h, :] = softmax(scale * q[b, h, :] . K_b[0:ctx_b, h / G, :]^T)
+ *                  . V_b[0:ctx_b, h / G, :],        G = num_q_heads / num_kv_heads
+ *   token t of sequence b lives at
+ *   cache[block_tables[b * table_stride + t / block_size], t % block_size, kvh, :].
+ *   ctx_b = context_lens[b] is read ON THE DEVICE; launch geometry depends
+ *   only on (bs, heads, num_splits), so the call is graph-capturable.
+ *   ctx_b == 0 -> the output row is zeros.  Table entries at or beyond
+ *   ceil(ctx_b / block_size) are never read (they may be -1 or 0 padding).
+ *
+ *   q   [bs, num_q_heads, head_dim], row stride q_row_stride, head stride head_dim
+ *   out [bs, num_q_heads, head_dim], contiguous
+ *   k_cache/v_cache [num_blocks, block_size, num_kv_heads, head_dim]:
+ *       cache_block_stride between blocks, cache_token_stride between tokens,
+ *       head stride head_dim, unit inner stride.
+ *   num_splits >= 1: split-KV (flash-decoding).  Each split takes an equal
+ *   share of the LIVE ctx_b (not of the table width).  num_splits > 1 needs a
+ *   workspace of nvllm_paged_decode_workspace_bytes(); the combine pass is
+ *   launched by this call.
+ *   Supported: head_dim == 128, G in {1,2,4,8}, block_size % 16 == 0.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride,
+                       const void* k_cache, const void* v_cache,
+                       int64_t cache_block_stride, int64_t cache_token_stride,
+                       const int32_t* block_tables, int64_t table_stride,
+                       const int32_t* context_lens,
+                       int32_t bs, int32_t num_q_heads, int32_t num_kv_heads,
+                       int32_t head_dim, int32_t block_size, float scale,
+                       int32_t num_splits, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* Bytes of split-KV workspace for the given geometry (0 when num_splits==1). */
+NVLLM_API size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads,
+                                          int32_t head_dim, int32_t num_splits);
+
+/* Host-side split heuristic (pure function, no CUDA calls besides an SM-count
+ * query when sm_count <= 0): picks num_splits from the launch-time-known
+ * geometry only — max_ctx is the table width * block_size under CUDA graphs.
+ * Returns the split count (>= 1). */
+NVLLM_API int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads,
+                                int32_t max_ctx, int32_t sm_count);
+
+/* Tuning hook: selects the decode tile variant (warps/stages/chunk) used by
+ * subsequent nvllm_paged_decode calls in this process; -1 restores the
+ * default.  Returns NVLLM_ERR_BAD_ARG for an unknown id. */
+NVLLM_API int nvllm_paged_decode_set_variant(int32_t variant);
+NVLLM_API int32_t nvllm_paged_decode_num_variants(void);
+
+/* ------------------------------------------------------------------------
+ * (3) varlen causal prefill with optional paged prefix (prefix cache).
+ *     reference: nanovllm/layers/attention.py:89-96
+ *
+ *   For sequence i: Lq_i = cu_seqlens_q[i+1]-cu_seqlens_q[i] new tokens,
+ *   Lk_i = cu_seqlens_k[i+1]-cu_seqlens_k[i] keys; query j attends keys
+ *   0 .. (Lk_i - Lq_i) + j  (causal mask aligned bottom-right, flash-attn
+ *   semantics).  Lq_i == 0 produces no rows.
+ *
+ *   block_tables == NULL: k/v are this step's dense [sum Lk, num_kv_heads,
+ *       head_dim] with row strides k_row_stride / v_row_stride.
+ *   block_tables != NULL: k/v are the paged caches
+ *       [num_blocks, block_size, num_kv_heads, head_dim]; k_row_stride /
+ *       v_row_stride are the TOKEN strides and cache_block_stride the block
+ *       stride; key t of sequence i is read from
+ *       block_tables[i * table_stride + t / block_size].
+ *   q   [sum Lq, num_q_heads, head_dim] with row stride q_row_stride
+ *   out [sum Lq, num_q_heads, head_dim] contiguous
+ *   max_seqlen_q bounds the grid (as in the reference call).
+ *   Supported: head_dim == 128, num_q_heads % num_kv_heads == 0.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride,
+                         const void* k, int64_t k_row_stride,
+                         const void* v, int64_t v_row_stride,
+                         int64_t cache_block_stride,
+                         const int32_t* cu_seqlens_q,
+                         const int32_t* cu_seqlens_k,
+                         int32_t batch, int32_t max_seqlen_q,
+                         int32_t max_seqlen_k,
+                         const int32_t* block_tables, int64_t table_stride,
+                         int32_t num_q_heads, int32_t num_kv_heads,
+                         int32_t head_dim, int32_t block_size, float scale,
+                         void* stream);
+
+/* Tuning hook: 0 = mma.sync path, 1 = tcgen05/TMEM path (when built),
+ * -1 = default. */
+NVLLM_API int nvllm_varlen_prefill_set_variant(int32_t variant);
+
+/* ------------------------------------------------------------------------
+ * (4) runner glue index math on the HOST (plain C, no CUDA): the integer
+ *     arithmetic of prepare_decode / prepare_prefill, so the Python glue can
+ *     fill persistent pinned staging buffers without per-step list building.
+ *     reference: nanovllm/engine/model_runner.py:244-269 and :212-221,
+ *                nanovllm/engine/sequence.py:53-65
+ * ---------------------------------------------------------------------- */
+
+/* prepare_decode for one sequence: given num_tokens (= len(seq)) and the id
+ * of its LAST block, the slot of the token being appended is
+ *   last_block * block_size + last_block_num_tokens - 1,
+ *   last_block_num_tokens = num_tokens - (ceil(num_tokens/block_size)-1)*block_size.
+ * Vectorised over n sequences. */
+NVLLM_API int nvllm_prepare_decode_slots(const int32_t* num_tokens,
+                               const int32_t* last_block, int32_t n,
+                               int32_t block_size, int32_t* slot_mapping_out);
+
+/* prepare_prefill slot ranges for one sequence: appends, for block index i in
+ * [num_cached_blocks, num_blocks), range(bt[i]*bs, bt[i]*bs + (bs or
+ * last_block_num_tokens)).  Returns the number of slots written, or a
+ * negative status on bad arguments / insufficient capacity. */
+NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
+                                    int32_t num_table_entries,
+                                    int32_t num_tokens,
+                                    int32_t num_cached_tokens,
+                                    int32_t block_size, int32_t* slots_out,
+                                    int64_t capacity);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NVLLM_ATTN_H_ */

@@ -1,0 +1,430 @@
+// Paged GQA decode attention (one query token per sequence) for sm_100a.
+// Replaces flash_attn_with_kvcache at reference nanovllm/layers/attention.py:97-101;
+// semantics restated from nanovllm/layers/attention_sdpa.py:122-182.
+//
+// HBM-bound: every (token, kv-head) K row and V row (256 B each) is read exactly once.
+// Algorithmic bytes per launch = sum_b ctx_b * Hkv * 512 + 2 * bs * Hq * 256 + 4*bs + 4*sum_b ceil(ctx_b/256).
+//
+// Design
+//  * grid (num_splits, Hkv, bs): a CTA owns one (sequence, kv head, split).  The split takes an
+//    equal share of the LIVE ctx_b read on the device, so launch geometry is capture-time constant
+//    while work stays balanced (flash-attn splits the table width instead).
+//  * inside the CTA each warp is an independent pipeline: it streams CHUNK-token slices of K and V
+//    (CHUNK x 512 B) with 16-byte cp.async into its private STAGES-deep shared-memory ring, indexed
+//    through block_tables, with no block-wide barrier in the main loop.
+//  * the G query heads sharing the kv head are the (zero-padded) 16 rows of an m16n8k16 bf16 MMA:
+//    S = Q.K^T and O += P.V run on the tensor cores with fp32 accumulation; online softmax between
+//    them uses warp shuffles only.
+//  * warps merge their (m, l, O) in shared memory once; with num_splits > 1 the CTA writes a
+//    normalised partial + log2-sum-exp and a small combine kernel merges the splits.
+#include "common.cuh"
+
+namespace nvllm {
+
+struct DecodeParams {
+  const __nv_bfloat16* q;
+  int64_t q_row_stride;
+  const __nv_bfloat16* k_cache;
+  const __nv_bfloat16* v_cache;
+  int64_t block_stride;  // elements between cache blocks
+  int64_t token_stride;  // elements between tokens inside a block
+  const int32_t* block_tables;
+  int64_t table_stride;
+  const int32_t* context_lens;
+  __nv_bfloat16* out;  // [bs, Hq, 128]
+  float* part_o;       // [bs, Hq, S, 128]
+  float* part_lse;     // [bs, Hq, S]   (log2 units)
+  int32_t num_q_heads;
+  int32_t group;       // G = Hq / Hkv
+  int32_t block_size;
+  int32_t num_splits;
+  float scale_log2;    // softmax scale * log2(e)
+};
+
+template <int CHUNK, int WARPS, int STAGES>
+struct DecodeCfg {
+  static constexpr int kChunk = CHUNK;
+  static constexpr int kWarps = WARPS;
+  static constexpr int kStages = STAGES;
+  static constexpr int kTileBytes = CHUNK * kRowBytes;          // K (or V) bytes of one chunk
+  static constexpr int kStageBytes = 2 * kTileBytes;            // K + V
+  static constexpr int kWarpBytes = STAGES * kStageBytes;
+  static constexpr int kPipeBytes = WARPS * kWarpBytes;
+  // merge scratch: per warp 8 rows x 128 fp32 + m[8] + l[8]
+  static constexpr int kMergeBytes = WARPS * (8 * kHeadDim * 4 + 64);
+  static constexpr int kSmemBytes = kPipeBytes > kMergeBytes ? kPipeBytes : kMergeBytes;
+};
+
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const DecodeParams p) {
+  constexpr int CHUNK = Cfg::kChunk;
+  constexpr int WARPS = Cfg::kWarps;
+  constexpr int STAGES = Cfg::kStages;
+  constexpr int NT = CHUNK / 8;    // S n-tiles (8 tokens each)
+  constexpr int KS = CHUNK / 16;   // PV k-steps (16 tokens each)
+  constexpr int PIECES = CHUNK * 16 / 32;  // 16-byte pieces per lane per tensor per chunk
+
+  extern __shared__ __align__(128) unsigned char smem[];
+
+  const int split = blockIdx.x;
+  const int kvh = blockIdx.y;
+  const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int G = p.group;
+
+  const int ctx = __ldg(p.context_lens + b);
+  const int n_chunks = (ctx + CHUNK - 1) / CHUNK;
+  const int per_split = (n_chunks + p.num_splits - 1) / p.num_splits;
+  const int c_begin = split * per_split;
+  const int c_end = min(c_begin + per_split, n_chunks);
+  // chunks of this warp: c_begin + warp + i * WARPS
+  const int n_my = (c_end - c_begin - warp + WARPS - 1) / WARPS;  // may be <= 0
+
+  // ---- Q fragments (A operand, rows >= G and rows 8..15 are zero) -------------------------
+  const int qrow = lane >> 2;
+  uint32_t qa0[8], qa2[8];
+  {
+    const bool live = qrow < G;
+    const __nv_bfloat16* qp =
+        p.q + static_cast<int64_t>(b) * p.q_row_stride + static_cast<int64_t>(kvh * G + (live ? qrow : 0)) * kHeadDim +
+        (lane & 3) * 2;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      qa0[ks] = live ? __ldg(reinterpret_cast<const uint32_t*>(qp + ks * 16)) : 0u;
+      qa2[ks] = live ? __ldg(reinterpret_cast<const uint32_t*>(qp + ks * 16 + 8)) : 0u;
+    }
+  }
+
+  float o[16][4];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+  float m_run = -INFINITY;  // running max of raw scores (row = lane>>2)
+  float l_run = 0.f;        // per-lane partial of the softmax denominator
+
+  unsigned char* my_smem = smem + warp * Cfg::kWarpBytes;
+  const uint32_t my_smem_u32 = smem_u32(my_smem);
+  const int32_t* table = p.block_tables + static_cast<int64_t>(b) * p.table_stride;
+  const int64_t head_off = static_cast<int64_t>(kvh) * kHeadDim;
+
+  // piece -> (token, 16-byte column) of the chunk: lanes 0..15 cover one 256 B row.
+  const int col16 = lane & 15;
+  const int tok_lo = lane >> 4;
+
+  auto issue = [&](int i, int page) {
+    const int chunk = c_begin + warp + i * WARPS;
+    const int t0 = chunk * CHUNK;
+    const int in_page = t0 % p.block_size;
+    const int64_t base = static_cast<int64_t>(page) * p.block_stride + head_off + col16 * 8;
+    const uint32_t sk = my_smem_u32 + (i % STAGES) * Cfg::kStageBytes;
+    const uint32_t sv = sk + Cfg::kTileBytes;
+#pragma unroll
+    for (int j = 0; j < PIECES; ++j) {
+      const int tok = j * 2 + tok_lo;
+      const uint32_t nbytes = (t0 + tok < ctx) ? 16u : 0u;
+      const int64_t off = base + static_cast<int64_t>(in_page + tok) * p.token_stride;
+      const uint32_t d = swz_off(tok, col16);
+      cp_async16(sk + d, p.k_cache + off, nbytes);
+      cp_async16(sv + d, p.v_cache + off, nbytes);
+    }
+  };
+  auto page_of = [&](int i) -> int {
+    if (i >= n_my) return 0;
+    const int chunk = c_begin + warp + i * WARPS;
+    return __ldg(table + (chunk * CHUNK) / p.block_size);
+  };
+
+  // ---- prologue: fill STAGES-1 stages -----------------------------------------------------
+  int page_next = page_of(0);
+#pragma unroll
+  for (int i = 0; i < STAGES - 1; ++i) {
+    const int page = page_next;
+    page_next = page_of(i + 1);
+    if (i < n_my) issue(i, page);
+    cp_async_commit();
+  }
+
+  for (int i = 0; i < n_my; ++i) {
+    {
+      const int nxt = i + STAGES - 1;
+      const int page = page_next;
+      page_next = page_of(nxt + 1);
+      if (nxt < n_my) issue(nxt, page);
+      cp_async_commit();
+    }
+    cp_async_wait<STAGES - 1>();
+    __syncwarp();
+
+    const uint32_t sk = my_smem_u32 + (i % STAGES) * Cfg::kStageBytes;
+    const uint32_t sv = sk + Cfg::kTileBytes;
+    const int t0 = (c_begin + warp + i * WARPS) * CHUNK;
+
+    // ---- S = Q . K^T  (16 x CHUNK) ---------------------------------------------------------
+    float s[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+    for (int kk2 = 0; kk2 < 4; ++kk2) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        uint32_t r0, r1, r2, r3;
+        ldmatrix_x4(r0, r1, r2, r3, sk + swz_off(nt * 8 + (lane & 7), kk2 * 4 + (lane >> 3)));
+        mma_bf16_16816(s[nt], qa0[kk2 * 2], 0u, qa2[kk2 * 2], 0u, r0, r1);
+        mma_bf16_16816(s[nt], qa0[kk2 * 2 + 1], 0u, qa2[kk2 * 2 + 1], 0u, r2, r3);
+      }
+    }
+
+    // ---- online softmax on rows 0..7 (this lane: row lane>>2, tokens nt*8 + (lane&3)*2 + {0,1})
+    float mx = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int t = t0 + nt * 8 + (lane & 3) * 2;
+      if (t >= ctx) s[nt][0] = -INFINITY;
+      if (t + 1 >= ctx) s[nt][1] = -INFINITY;
+      mx = fmaxf(mx, fmaxf(s[nt][0], s[nt][1]));
+    }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m_run, mx);  // finite: every chunk holds at least one live token
+    const float alpha = fast_exp2((m_run - m_new) * p.scale_log2);
+    const float m_scaled = m_new * p.scale_log2;
+    m_run = m_new;
+    float psum = 0.f;
+    uint32_t pa0[KS], pa2[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const float p00 = fast_exp2(s[2 * ks][0] * p.scale_log2 - m_scaled);
+      const float p01 = fast_exp2(s[2 * ks][1] * p.scale_log2 - m_scaled);
+      const float p10 = fast_exp2(s[2 * ks + 1][0] * p.scale_log2 - m_scaled);
+      const float p11 = fast_exp2(s[2 * ks + 1][1] * p.scale_log2 - m_scaled);
+      psum += (p00 + p01) + (p10 + p11);
+      pa0[ks] = pack_bf16x2(p00, p01);
+      pa2[ks] = pack_bf16x2(p10, p11);
+    }
+    l_run = l_run * alpha + psum;
+#pragma unroll
+    for (int i2 = 0; i2 < 16; ++i2) {
+      o[i2][0] *= alpha;
+      o[i2][1] *= alpha;
+    }
+
+    // ---- O += P . V  (16 x 128) ------------------------------------------------------------
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int c2 = 0; c2 < 8; ++c2) {
+        uint32_t r0, r1, r2, r3;
+        const int j = lane >> 3;
+        ldmatrix_x4_trans(r0, r1, r2, r3, sv + swz_off(ks * 16 + (j & 1) * 8 + (lane & 7), c2 * 2 + (j >> 1)));
+        mma_bf16_16816(o[c2 * 2], pa0[ks], 0u, pa2[ks], 0u, r0, r1);
+        mma_bf16_16816(o[c2 * 2 + 1], pa0[ks], 0u, pa2[ks], 0u, r2, r3);
+      }
+    }
+    __syncwarp();
+  }
+  cp_async_wait<0>();
+
+  // ---- merge the warps of this CTA ---------------------------------------------------------
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+  l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+  __syncthreads();  // every warp is done with its pipeline buffers
+  float* mo = reinterpret_cast<float*>(smem);                  // [WARPS][8][128]
+  float* mm = mo + WARPS * 8 * kHeadDim;                       // [WARPS][8]
+  float* ml = mm + WARPS * 8;                                  // [WARPS][8]
+  if (qrow < G) {
+    float* dst = mo + (warp * 8 + qrow) * kHeadDim + (lane & 3) * 2;
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) *reinterpret_cast<float2*>(dst + nt * 8) = make_float2(o[nt][0], o[nt][1]);
+    if ((lane & 3) == 0) {
+      mm[warp * 8 + qrow] = m_run;
+      ml[warp * 8 + qrow] = l_run;
+    }
+  }
+  __syncthreads();
+
+  for (int idx = threadIdx.x; idx < G * kHeadDim; idx += WARPS * 32) {
+    const int row = idx >> 7;
+    const int d = idx & (kHeadDim - 1);
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) M = fmaxf(M, mm[w * 8 + row]);
+    float num = 0.f, den = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int w = 0; w < WARPS; ++w) {
+        const float wgt = fast_exp2((mm[w * 8 + row] - M) * p.scale_log2);
+        num += wgt * mo[(w * 8 + row) * kHeadDim + d];
+        den += wgt * ml[w * 8 + row];
+      }
+    }
+    const float val = den > 0.f ? num / den : 0.f;
+    const int h = kvh * G + row;
+    if (p.num_splits == 1) {
+      p.out[(static_cast<int64_t>(b) * p.num_q_heads + h) * kHeadDim + d] = __float2bfloat16_rn(val);
+    } else {
+      const int64_t slot = (static_cast<int64_t>(b) * p.num_q_heads + h) * p.num_splits + split;
+      p.part_o[slot * kHeadDim + d] = val;
+      if (d == 0) p.part_lse[slot] = den > 0.f ? M * p.scale_log2 + fast_log2(den) : -INFINITY;
+    }
+  }
+}
+
+// Merge the split partials: out = sum_s 2^(lse_s - L) O_s / sum_s 2^(lse_s - L).
+// grid (bs * Hq), block 128 (one thread per head-dim element).
+__global__ void __launch_bounds__(kHeadDim) paged_decode_combine_kernel(const float* __restrict__ part_o,
+                                                                        const float* __restrict__ part_lse,
+                                                                        __nv_bfloat16* __restrict__ out,
+                                                                        int32_t num_splits) {
+  const int64_t row = blockIdx.x;
+  const int d = threadIdx.x;
+  const float* lse = part_lse + row * num_splits;
+  float L = -INFINITY;
+  for (int s = 0; s < num_splits; ++s) L = fmaxf(L, __ldg(lse + s));
+  float num = 0.f, den = 0.f;
+  if (L > -INFINITY) {
+    const float* po = part_o + row * num_splits * kHeadDim + d;
+    for (int s = 0; s < num_splits; ++s) {
+      const float w = fast_exp2(__ldg(lse + s) - L);
+      num += w * __ldg(po + static_cast<int64_t>(s) * kHeadDim);
+      den += w;
+    }
+  }
+  out[row * kHeadDim + d] = __float2bfloat16_rn(den > 0.f ? num / den : 0.f);
+}
+
+// ---- variants -------------------------------------------------------------------------------
+using Cfg0 = DecodeCfg<16, 4, 3>;  //  96 KB: two CTAs per SM
+using Cfg1 = DecodeCfg<16, 4, 4>;  // 128 KB
+using Cfg2 = DecodeCfg<16, 8, 3>;  // 192 KB
+using Cfg3 = DecodeCfg<32, 4, 3>;  // 192 KB
+using Cfg4 = DecodeCfg<32, 2, 3>;  //  96 KB: two CTAs per SM
+using Cfg5 = DecodeCfg<16, 2, 6>;  //  96 KB: two CTAs per SM
+using Cfg6 = DecodeCfg<16, 4, 6>;  // 192 KB
+using Cfg7 = DecodeCfg<32, 4, 2>;  // 128 KB
+constexpr int kNumVariants = 8;
+constexpr int kDefaultVariant = 0;
+static int g_variant = kDefaultVariant;
+
+template <class Cfg>
+static cudaError_t launch_decode(const DecodeParams& p, int bs, int hkv, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::kSmemBytes);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid(p.num_splits, hkv, bs);
+  paged_decode_kernel<Cfg><<<grid, Cfg::kWarps * 32, Cfg::kSmemBytes, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace nvllm
+
+extern "C" {
+
+size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads, int32_t head_dim, int32_t num_splits) {
+  if (bs <= 0 || num_q_heads <= 0 || head_dim <= 0 || num_splits <= 1) return 0;
+  const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
+  return rows * head_dim * sizeof(float) + rows * sizeof(float);
+}
+
+int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ctx, int32_t sm_count) {
+  if (bs <= 0 || num_kv_heads <= 0 || max_ctx <= 0) return 1;
+  if (sm_count <= 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    sm_count = n;
+  }
+  // Cost model in token units: every SM streams its CTAs' tokens back to back; a split adds a
+  // fixed overhead (prologue latency + merge + its share of the combine pass).
+  const int64_t items = static_cast<int64_t>(bs) * num_kv_heads;
+  const int64_t kOverheadTokens = 96;
+  const int max_splits = max_ctx / 64 > 1 ? (max_ctx / 64 < 64 ? max_ctx / 64 : 64) : 1;
+  int best = 1;
+  int64_t best_cost = INT64_MAX;
+  for (int s = 1; s <= max_splits; ++s) {
+    const int64_t per_sm = (items * s + sm_count - 1) / sm_count;
+    const int64_t cost = per_sm * ((max_ctx + s - 1) / s + kOverheadTokens) + (s > 1 ? kOverheadTokens : 0);
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = s;
+    }
+  }
+  return best;
+}
+
+int nvllm_paged_decode_set_variant(int32_t variant) {
+  if (variant == -1) variant = nvllm::kDefaultVariant;
+  if (variant < 0 || variant >= nvllm::kNumVariants) return NVLLM_ERR_BAD_ARG;
+  nvllm::g_variant = variant;
+  return NVLLM_OK;
+}
+int32_t nvllm_paged_decode_num_variants(void) { return nvllm::kNumVariants; }
+
+int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
+                       int64_t cache_block_stride, int64_t cache_token_stride, const int32_t* block_tables,
+                       int64_t table_stride, const int32_t* context_lens, int32_t bs, int32_t num_q_heads,
+                       int32_t num_kv_heads, int32_t head_dim, int32_t block_size, float scale, int32_t num_splits,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace nvllm;
+  if (bs < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || block_size <= 0 || num_splits < 1)
+    return NVLLM_ERR_BAD_ARG;
+  if (bs == 0) return NVLLM_OK;
+  if (!out || !q || !k_cache || !v_cache || !block_tables || !context_lens) return NVLLM_ERR_BAD_ARG;
+  if (head_dim != kHeadDim || num_q_heads % num_kv_heads != 0 || block_size % 32 != 0) return NVLLM_ERR_UNSUPPORTED;
+  const int G = num_q_heads / num_kv_heads;
+  if (G > 8) return NVLLM_ERR_UNSUPPORTED;
+  if (bs > 65535 || num_kv_heads > 65535) return NVLLM_ERR_UNSUPPORTED;
+  if (q_row_stride < static_cast<int64_t>(num_q_heads) * head_dim || table_stride < 0) return NVLLM_ERR_BAD_ARG;
+  if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache) || (q_row_stride & 7) ||
+      (cache_block_stride & 7) || (cache_token_stride & 7))
+    return NVLLM_ERR_ALIGNMENT;
+  const size_t need = nvllm_paged_decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits);
+  if (num_splits > 1 && (!workspace || workspace_bytes < need || !aligned16(workspace))) return NVLLM_ERR_WORKSPACE;
+
+  DecodeParams p;
+  p.q = static_cast<const __nv_bfloat16*>(q);
+  p.q_row_stride = q_row_stride;
+  p.k_cache = static_cast<const __nv_bfloat16*>(k_cache);
+  p.v_cache = static_cast<const __nv_bfloat16*>(v_cache);
+  p.block_stride = cache_block_stride;
+  p.token_stride = cache_token_stride;
+  p.block_tables = block_tables;
+  p.table_stride = table_stride;
+  p.context_lens = context_lens;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.part_o = static_cast<float*>(workspace);
+  p.part_lse = num_splits > 1 ? p.part_o + static_cast<size_t>(bs) * num_q_heads * num_splits * head_dim : nullptr;
+  p.num_q_heads = num_q_heads;
+  p.group = G;
+  p.block_size = block_size;
+  p.num_splits = num_splits;
+  p.scale_log2 = scale * kLog2e;
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  switch (g_variant) {
+    case 0: e = launch_decode<Cfg0>(p, bs, num_kv_heads, st); break;
+    case 1: e = launch_decode<Cfg1>(p, bs, num_kv_heads, st); break;
+    case 2: e = launch_decode<Cfg2>(p, bs, num_kv_heads, st); break;
+    case 3: e = launch_decode<Cfg3>(p, bs, num_kv_heads, st); break;
+    case 4: e = launch_decode<Cfg4>(p, bs, num_kv_heads, st); break;
+    case 5: e = launch_decode<Cfg5>(p, bs, num_kv_heads, st); break;
+    case 6: e = launch_decode<Cfg6>(p, bs, num_kv_heads, st); break;
+    default: e = launch_decode<Cfg7>(p, bs, num_kv_heads, st); break;
+  }
+  note_launch();
+  if (e != cudaSuccess) return record_cuda_error(e);
+  if (num_splits > 1) {
+    paged_decode_combine_kernel<<<static_cast<unsigned>(bs * num_q_heads), kHeadDim, 0, st>>>(
+        p.part_o, p.part_lse, p.out, num_splits);
+    note_launch();
+    e = cudaGetLastError();
+  }
+  return record_cuda_error(e);
+}
+
+}  // extern "C"

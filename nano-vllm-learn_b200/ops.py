@@ -1,0 +1,164 @@
+"""Torch-tensor front end of the C ABI: pointer/stride extraction only, no arithmetic on the host.
+
+Function names and argument meaning follow the reference operators they replace:
+  store_kvcache           nanovllm/layers/attention.py:44-55
+  flash_attn_with_kvcache nanovllm/layers/attention.py:99-101  (paged decode)
+  flash_attn_varlen_func  nanovllm/layers/attention.py:93-96   (varlen prefill, optional block_table)
+Every function requires CUDA tensors and the built library; there is no fallback path.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+_PLAN_CACHE: dict[tuple[int, int, int], int] = {}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("nvllm cuda attention backend needs CUDA tensors (no CPU fallback)")
+
+
+def launch_count() -> int:
+    return int(_lib.load().nvllm_launch_count())
+
+
+def reset_launch_count() -> None:
+    _lib.load().nvllm_reset_launch_count()
+
+
+def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                  slot_mapping: torch.Tensor) -> None:
+    """key/value [N, Hkv, D] (arbitrary row stride) -> k_cache/v_cache [num_blocks, block, Hkv, D]."""
+    lib = _lib.load()
+    _require_cuda(key, value, k_cache, v_cache, slot_mapping)
+    n, num_kv_heads, head_dim = key.shape
+    row = num_kv_heads * head_dim
+    # same layout asserts as the reference (attention.py:51-54)
+    assert key.stride(-1) == 1 and value.stride(-1) == 1
+    assert key.stride(1) == head_dim and value.stride(1) == head_dim
+    assert k_cache.stride(1) == row and v_cache.stride(1) == row
+    assert slot_mapping.numel() == n
+    assert slot_mapping.dtype == torch.int32 and slot_mapping.is_contiguous()
+    assert key.dtype == value.dtype == k_cache.dtype == v_cache.dtype
+    assert k_cache.stride(0) == k_cache.size(1) * row and v_cache.stride(0) == v_cache.size(1) * row
+    if n == 0:
+        return
+    st = lib.nvllm_store_kvcache(key.data_ptr(), key.stride(0), value.data_ptr(), value.stride(0),
+                                 k_cache.data_ptr(), v_cache.data_ptr(), slot_mapping.data_ptr(),
+                                 n, num_kv_heads, head_dim, key.element_size(), _stream())
+    _lib.check(st, "store_kvcache")
+
+
+def plan_num_splits(bs: int, num_kv_heads: int, max_ctx: int) -> int:
+    key = (bs, num_kv_heads, max_ctx)
+    s = _PLAN_CACHE.get(key)
+    if s is None:
+        s = int(_lib.load().nvllm_paged_decode_plan(bs, num_kv_heads, max_ctx, 0))
+        _PLAN_CACHE[key] = s
+    return s
+
+
+def decode_workspace_bytes(bs: int, num_q_heads: int, head_dim: int, num_splits: int) -> int:
+    return int(_lib.load().nvllm_paged_decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits))
+
+
+def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                            cache_seqlens: torch.Tensor, block_table: torch.Tensor,
+                            softmax_scale: Optional[float] = None, causal: bool = True,
+                            num_splits: int = 0, out: Optional[torch.Tensor] = None,
+                            workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Paged decode.  q [bs, 1, Hq, D] (or [bs, Hq, D]); returns the same shape.
+
+    `causal` is accepted for signature parity; with one query token the bottom-right causal mask is
+    a no-op.  num_splits=0 lets the library plan from (bs, Hkv, table width) only.
+    """
+    lib = _lib.load()
+    _require_cuda(q, k_cache, v_cache, cache_seqlens, block_table)
+    squeeze = q.dim() == 4
+    if squeeze:
+        assert q.shape[1] == 1, "Decode stage should have seq_len=1"
+        q3 = q[:, 0]
+    else:
+        q3 = q
+    bs, num_q_heads, head_dim = q3.shape
+    _, block_size, num_kv_heads, _ = k_cache.shape
+    assert q3.dtype == torch.bfloat16 and k_cache.dtype == torch.bfloat16 and v_cache.dtype == torch.bfloat16
+    assert q3.stride(-1) == 1 and q3.stride(1) == head_dim
+    assert k_cache.stride(-1) == 1 and k_cache.stride(2) == head_dim
+    assert v_cache.stride() == k_cache.stride() and v_cache.shape == k_cache.shape
+    assert cache_seqlens.dtype == torch.int32 and cache_seqlens.is_contiguous() and cache_seqlens.numel() == bs
+    assert block_table.dtype == torch.int32 and block_table.stride(-1) == 1 and block_table.size(0) == bs
+    if softmax_scale is None:
+        softmax_scale = head_dim ** -0.5
+    if num_splits <= 0:
+        num_splits = plan_num_splits(bs, num_kv_heads, block_table.size(1) * block_size)
+    if out is None:
+        out = torch.empty((bs, num_q_heads, head_dim), dtype=q.dtype, device=q.device)
+    ws_bytes = decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits)
+    ws_ptr = 0
+    if ws_bytes:
+        if workspace is None or workspace.numel() * workspace.element_size() < ws_bytes:
+            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)
+        ws_ptr = workspace.data_ptr()
+        ws_bytes = workspace.numel() * workspace.element_size()
+    st = lib.nvllm_paged_decode(out.data_ptr(), q3.data_ptr(), q3.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                                k_cache.stride(0), k_cache.stride(1), block_table.data_ptr(), block_table.stride(0),
+                                cache_seqlens.data_ptr(), bs, num_q_heads, num_kv_heads, head_dim, block_size,
+                                float(softmax_scale), num_splits, ws_ptr, ws_bytes, _stream())
+    _lib.check(st, "paged_decode")
+    return out.unsqueeze(1) if squeeze else out
+
+
+def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, max_seqlen_q: int,
+                           cu_seqlens_q: torch.Tensor, max_seqlen_k: int, cu_seqlens_k: torch.Tensor,
+                           softmax_scale: Optional[float] = None, causal: bool = True,
+                           block_table: Optional[torch.Tensor] = None,
+                           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Varlen causal prefill.  q [sum Lq, Hq, D]; k/v dense [sum Lk, Hkv, D] or, with block_table,
+    the paged caches [num_blocks, block, Hkv, D].  Mask is bottom-right aligned (flash-attn)."""
+    lib = _lib.load()
+    _require_cuda(q, k, v, cu_seqlens_q, cu_seqlens_k, block_table)
+    if not causal:
+        raise ValueError("the cuda backend implements the causal prefill the reference calls (causal=True)")
+    if cu_seqlens_q is None:
+        raise ValueError("cu_seqlens_q must be provided for varlen attention")
+    total_q, num_q_heads, head_dim = q.shape
+    assert q.dtype == torch.bfloat16 and k.dtype == torch.bfloat16 and v.dtype == torch.bfloat16
+    assert q.stride(-1) == 1 and q.stride(1) == head_dim
+    assert cu_seqlens_q.dtype == torch.int32 and cu_seqlens_k.dtype == torch.int32
+    assert cu_seqlens_q.is_contiguous() and cu_seqlens_k.is_contiguous()
+    batch = cu_seqlens_q.numel() - 1
+    if softmax_scale is None:
+        softmax_scale = head_dim ** -0.5
+    if out is None:
+        out = torch.empty((total_q, num_q_heads, head_dim), dtype=q.dtype, device=q.device)
+    if total_q == 0 or batch <= 0:
+        return out
+    if block_table is not None:
+        assert k.dim() == 4 and v.shape == k.shape and v.stride() == k.stride()
+        assert block_table.dtype == torch.int32 and block_table.stride(-1) == 1 and block_table.size(0) == batch
+        _, block_size, num_kv_heads, _ = k.shape
+        assert k.stride(-1) == 1 and k.stride(2) == head_dim
+        k_row, v_row, blk = k.stride(1), v.stride(1), k.stride(0)
+        bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
+    else:
+        assert k.dim() == 3 and v.dim() == 3
+        num_kv_heads = k.shape[1]
+        assert k.stride(-1) == 1 and k.stride(1) == head_dim and v.stride(-1) == 1 and v.stride(1) == head_dim
+        k_row, v_row, blk = k.stride(0), v.stride(0), 0
+        block_size, bt_ptr, bt_stride = 0, 0, 0
+    st = lib.nvllm_varlen_prefill(out.data_ptr(), q.data_ptr(), q.stride(0), k.data_ptr(), k_row, v.data_ptr(), v_row,
+                                  blk, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), batch, int(max_seqlen_q),
+                                  int(max_seqlen_k), bt_ptr, bt_stride, num_q_heads, num_kv_heads, head_dim,
+                                  block_size, float(softmax_scale), _stream())
+    _lib.check(st, "varlen_prefill")
+    return out

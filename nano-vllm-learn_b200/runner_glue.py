@@ -1,0 +1,335 @@
+"""Runner glue for the cuda attention backend: prepare_prefill / prepare_decode / CUDA-graph capture.
+
+Re-implements, bit-identically in every tensor it publishes, the glue of the reference
+`nanovllm/engine/model_runner.py`:
+    prepare_block_tables :160-169     prepare_prefill :171-242     prepare_decode :244-269
+    run_model (graph replay) :278-303   capture_cudagraph :316-370
+B200-first differences (host side only, results unchanged):
+  * persistent pinned staging + ONE packed host->device copy per step instead of five pinned
+    allocations and five copies; index math for slots runs in C (nvllm_prepare_*_slots);
+  * in graph mode the metadata is staged directly in the captured buffers' layout (zero-padded
+    rows, -1-padded table columns inside the live width, exactly what `zero_()` + row copies
+    produce in the reference), so replay needs no extra device ops;
+  * a small ring of staging slots guarded by CUDA events keeps worker ranks (which never sync with
+    the host) from overwriting a slot whose copy is still in flight.
+The engine-facing quirks are kept on purpose: decode `positions = len(seq)` (model_runner.py:251),
+zero padding of graph rows (:291-293), `block_tables` only when a prefix hit exists (:225-232).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Callable, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_I32P = ctypes.POINTER(ctypes.c_int32)
+
+
+def _i32ptr(a: np.ndarray):
+    return a.ctypes.data_as(_I32P)
+
+
+class _Slot:
+    """One pinned staging slot + its typed numpy view and the event that guards reuse."""
+
+    def __init__(self, nbytes: int, pinned: bool):
+        self.host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=pinned)
+        self.np = self.host.numpy()
+        self.event = torch.cuda.Event() if pinned else None
+
+    def wait(self):
+        if self.event is not None:
+            self.event.synchronize()
+
+    def mark(self):
+        if self.event is not None:
+            self.event.record()
+
+
+def _align(n: int, a: int = 16) -> int:
+    return (n + a - 1) // a * a
+
+
+class RunnerGlue:
+    """Host-side metadata staging for one rank.  `set_context` is the engine's context setter."""
+
+    RING = 3
+
+    def __init__(self, block_size: int, max_num_seqs: int, max_model_len: int, max_num_batched_tokens: int,
+                 device, set_context: Callable, pad_slot: int = 0):
+        self.block_size = block_size
+        self.max_bs = max_num_seqs
+        self.max_blocks = (max_model_len + block_size - 1) // block_size
+        self.max_tokens = max_num_batched_tokens
+        self.device = torch.device(device)
+        self.pinned = self.device.type == "cuda"
+        self.set_context = set_context
+        self.pad_slot = pad_slot  # 0 = reference behaviour (model_runner.py:291-293); -1 = skip padded rows
+        self.lib = _lib.load()
+        # decode: ids i64 | pos i64 | slots i32 | lens i32 | tables i32[bs, W]
+        self._dec_bytes = self._decode_layout(self.max_bs, self.max_blocks)[-1]
+        # prefill: ids i64[T] | pos i64[T] | slots i32[T] | cu_q i32[B+1] | cu_k i32[B+1] | tables i32[B, W]
+        t, b = self.max_tokens, self.max_bs
+        self._pre_bytes = _align(8 * t) * 2 + _align(4 * t) + 2 * _align(4 * (b + 1)) + _align(4 * b * self.max_blocks)
+        nbytes = max(self._dec_bytes, self._pre_bytes)
+        self._ring = [_Slot(nbytes, self.pinned) for _ in range(self.RING)]
+        self._turn = 0
+        self.dev = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+        self._scratch_len = np.zeros(self.max_bs, dtype=np.int32)
+        self._scratch_last = np.zeros(self.max_bs, dtype=np.int32)
+        self.graph_bs: Optional[list[int]] = None   # set by capture; enables the bucketed decode layout
+
+    # ------------------------------------------------------------------ layouts
+    @staticmethod
+    def _decode_layout(gbs: int, width: int):
+        o_ids = 0
+        o_pos = o_ids + _align(8 * gbs)
+        o_slot = o_pos + _align(8 * gbs)
+        o_len = o_slot + _align(4 * gbs)
+        o_tab = o_len + _align(4 * gbs)
+        end = o_tab + _align(4 * gbs * width)
+        return o_ids, o_pos, o_slot, o_len, o_tab, end
+
+    def _typed(self, buf, off: int, count: int, dtype):
+        """Typed view [count] at byte offset `off` of a uint8 numpy array or torch tensor."""
+        if isinstance(buf, np.ndarray):
+            return buf[off:off + count * np.dtype(dtype).itemsize].view(dtype)
+        tdt = {np.int64: torch.int64, np.int32: torch.int32}[dtype]
+        return buf[off:off + count * np.dtype(dtype).itemsize].view(tdt)
+
+    def decode_views(self, buf, gbs: int, width: int):
+        o_ids, o_pos, o_slot, o_len, o_tab, _ = self._decode_layout(gbs, width)
+        ids = self._typed(buf, o_ids, gbs, np.int64)
+        pos = self._typed(buf, o_pos, gbs, np.int64)
+        slots = self._typed(buf, o_slot, gbs, np.int32)
+        lens = self._typed(buf, o_len, gbs, np.int32)
+        tab = self._typed(buf, o_tab, gbs * width, np.int32)
+        tab = tab.reshape(gbs, width) if isinstance(tab, np.ndarray) else tab.view(gbs, width)
+        return ids, pos, slots, lens, tab
+
+    def _next_slot(self) -> _Slot:
+        slot = self._ring[self._turn]
+        self._turn = (self._turn + 1) % self.RING
+        slot.wait()
+        return slot
+
+    def _upload(self, slot: _Slot, nbytes: int):
+        self.dev[:nbytes].copy_(slot.host[:nbytes], non_blocking=True)
+        slot.mark()
+
+    # ------------------------------------------------------------------ reference: model_runner.py:160-169
+    def prepare_block_tables(self, seqs: Sequence) -> torch.Tensor:
+        width = max(len(s.block_table) for s in seqs)
+        n = len(seqs)
+        slot = self._next_slot()
+        tab = slot.np[:4 * n * width].view(np.int32).reshape(n, width)
+        tab.fill(-1)
+        for i, s in enumerate(seqs):
+            bt = s.block_table
+            tab[i, :len(bt)] = bt
+        # standalone use only (prepare_prefill/prepare_decode stage their tables inline): fresh device tensor
+        out = torch.empty((n, width), dtype=torch.int32, device=self.device)
+        out.copy_(slot.host[:4 * n * width].view(torch.int32).view(n, width), non_blocking=True)
+        slot.mark()
+        return out
+
+    # ------------------------------------------------------------------ reference: model_runner.py:171-242
+    def prepare_prefill(self, seqs: Sequence):
+        bsz = self.block_size
+        n = len(seqs)
+        total_q = sum(len(s) - s.num_cached_tokens for s in seqs)
+        width = max(len(s.block_table) for s in seqs) if n else 0
+        o_ids = 0
+        o_pos = o_ids + _align(8 * total_q)
+        o_slot = o_pos + _align(8 * total_q)
+        # slots of a sequence cover its uncached BLOCKS (>= its uncached tokens only if cached is block aligned,
+        # which BlockManager guarantees), so total_q bounds the count
+        o_cuq = o_slot + _align(4 * total_q)
+        o_cuk = o_cuq + _align(4 * (n + 1))
+        o_tab = o_cuk + _align(4 * (n + 1))
+        end = o_tab + _align(4 * n * width)
+        if end > self.dev.numel():
+            raise ValueError("prefill batch exceeds max_num_batched_tokens/max_num_seqs staging capacity")
+        slot = self._next_slot()
+        h = slot.np
+        ids = h[o_ids:o_ids + 8 * total_q].view(np.int64)
+        pos = h[o_pos:o_pos + 8 * total_q].view(np.int64)
+        slots = h[o_slot:o_slot + 4 * total_q].view(np.int32)
+        cu_q = h[o_cuq:o_cuq + 4 * (n + 1)].view(np.int32)
+        cu_k = h[o_cuk:o_cuk + 4 * (n + 1)].view(np.int32)
+        cu_q[0] = cu_k[0] = 0
+        max_q = max_k = 0
+        tq = 0
+        n_slots = 0
+        for i, s in enumerate(seqs):
+            seqlen = len(s)
+            cached = s.num_cached_tokens
+            lq = seqlen - cached
+            ids[tq:tq + lq] = s[cached:]
+            pos[tq:tq + lq] = np.arange(cached, seqlen, dtype=np.int64)
+            tq += lq
+            cu_q[i + 1] = cu_q[i] + lq
+            cu_k[i + 1] = cu_k[i] + seqlen
+            max_q = max(max_q, lq)
+            max_k = max(max_k, seqlen)
+            bt = s.block_table
+            if not bt:
+                continue  # warmup sequences have no blocks (model_runner.py:209-210)
+            bt_np = np.asarray(bt, dtype=np.int32)
+            wrote = self.lib.nvllm_prepare_prefill_slots(_i32ptr(bt_np), len(bt), seqlen, cached, bsz,
+                                                         _i32ptr(slots[n_slots:]) if total_q > n_slots else None,
+                                                         total_q - n_slots)
+            if wrote < 0:
+                raise AssertionError(f"prepare_prefill slot math failed with status {-wrote}")
+            n_slots += int(wrote)
+        has_prefix = int(cu_k[n]) > int(cu_q[n])
+        if has_prefix:
+            tab = h[o_tab:o_tab + 4 * n * width].view(np.int32).reshape(n, width)
+            tab.fill(-1)
+            for i, s in enumerate(seqs):
+                bt = s.block_table
+                tab[i, :len(bt)] = bt
+        self._upload(slot, end if has_prefix else o_tab)
+        d = self.dev
+        d_ids = d[o_ids:o_ids + 8 * total_q].view(torch.int64)
+        d_pos = d[o_pos:o_pos + 8 * total_q].view(torch.int64)
+        d_slots = d[o_slot:o_slot + 4 * n_slots].view(torch.int32)
+        d_cuq = d[o_cuq:o_cuq + 4 * (n + 1)].view(torch.int32)
+        d_cuk = d[o_cuk:o_cuk + 4 * (n + 1)].view(torch.int32)
+        d_tab = d[o_tab:o_tab + 4 * n * width].view(torch.int32).view(n, width) if has_prefix else None
+        self.set_context(True, d_cuq, d_cuk, max_q, max_k, d_slots, None, d_tab)
+        return d_ids, d_pos
+
+    # ------------------------------------------------------------------ reference: model_runner.py:244-269
+    def decode_bucket(self, bs: int) -> Optional[int]:
+        """Captured graph batch size that serves `bs` (model_runner.py:288), None -> eager."""
+        if not self.graph_bs or bs > self.graph_bs[-1]:
+            return None
+        return next(x for x in self.graph_bs if x >= bs)
+
+    def prepare_decode(self, seqs: Sequence):
+        bsz = self.block_size
+        bs = len(seqs)
+        width = max(len(s.block_table) for s in seqs)
+        gbs = self.decode_bucket(bs)
+        if gbs is None:          # eager: tight [bs, width] table, -1 padded (prepare_block_tables)
+            rows, cols = bs, width
+        else:                    # graph: captured [gbs, max_blocks] layout, zero padded outside [:bs, :width]
+            rows, cols = gbs, self.max_blocks
+        lay = self._decode_layout(rows, cols)
+        slot = self._next_slot()
+        ids, pos, slots, lens, tab = self.decode_views(slot.np, rows, cols)
+        last = self._scratch_last
+        if gbs is not None:
+            tab.fill(0)
+            ids[bs:] = 0
+            pos[bs:] = 0
+            lens[bs:] = 0
+            slots[bs:] = self.pad_slot
+            tab[:bs, :width] = -1
+        else:
+            tab.fill(-1)
+        for i, s in enumerate(seqs):
+            n = len(s)
+            bt = s.block_table
+            ids[i] = s.last_token
+            pos[i] = n          # sic: the reference feeds len(seq), not len(seq)-1 (model_runner.py:251)
+            lens[i] = n
+            last[i] = bt[-1]
+            tab[i, :len(bt)] = bt
+        st = self.lib.nvllm_prepare_decode_slots(_i32ptr(lens), _i32ptr(last), bs, bsz, _i32ptr(slots))
+        if st != 0:
+            raise AssertionError("prepare_decode slot math failed")
+        self._upload(slot, lay[-1])
+        d_ids, d_pos, d_slots, d_lens, d_tab = self.decode_views(self.dev, rows, cols)
+        self.set_context(False, slot_mapping=d_slots[:bs], context_lens=d_lens[:bs],
+                         block_tables=d_tab[:bs, :width])
+        return d_ids[:bs], d_pos[:bs]
+
+    # ------------------------------------------------------------------ reference: model_runner.py:316-370
+    def graph_buffers(self, gbs: int):
+        """Device views a graph of batch size `gbs` is captured on (and later replayed from)."""
+        return self.decode_views(self.dev, gbs, self.max_blocks)
+
+
+# ---------------------------------------------------------------------- engine integration
+def install(model_runner_cls, set_context: Callable, get_context: Callable, reset_context: Callable) -> None:
+    """Swap the glue methods of the host engine's ModelRunner for the cuda backend.
+
+    Called from the reference-side binding: the original methods stay in place for
+    every other backend; dispatch is on `hf_config.attn_backend == "cuda"` per instance.
+    """
+    orig = {name: getattr(model_runner_cls, name) for name in
+            ("prepare_block_tables", "prepare_prefill", "prepare_decode", "run_model", "capture_cudagraph")}
+
+    def _is_cuda(self) -> bool:
+        return getattr(self.config.hf_config, "attn_backend", "flash") == "cuda"
+
+    def _glue(self) -> RunnerGlue:
+        g = getattr(self, "_nvllm_glue", None)
+        if g is None:
+            cfg = self.config
+            import os
+            g = RunnerGlue(self.block_size, cfg.max_num_seqs, cfg.max_model_len, cfg.max_num_batched_tokens,
+                           torch.device("cuda", torch.cuda.current_device()), set_context,
+                           pad_slot=int(os.environ.get("NVLLM_PAD_SLOT", "0")))
+            self._nvllm_glue = g
+        return g
+
+    def prepare_block_tables(self, seqs):
+        return _glue(self).prepare_block_tables(seqs) if _is_cuda(self) else orig["prepare_block_tables"](self, seqs)
+
+    def prepare_prefill(self, seqs):
+        return _glue(self).prepare_prefill(seqs) if _is_cuda(self) else orig["prepare_prefill"](self, seqs)
+
+    def prepare_decode(self, seqs):
+        return _glue(self).prepare_decode(seqs) if _is_cuda(self) else orig["prepare_decode"](self, seqs)
+
+    @torch.inference_mode()
+    def run_model(self, input_ids, positions, is_prefill):
+        if not _is_cuda(self):
+            return orig["run_model"](self, input_ids, positions, is_prefill)
+        bs = input_ids.size(0)
+        g = _glue(self)
+        gbs = None if (is_prefill or self.enforce_eager) else g.decode_bucket(bs)
+        if gbs is None:
+            return self.model.compute_logits(self.model(input_ids, positions))
+        # prepare_decode already staged ids/positions/context in the captured buffers of bucket `gbs`
+        self.graphs[gbs].replay()
+        return self.model.compute_logits(self.graph_vars["outputs"][:bs])
+
+    @torch.inference_mode()
+    def capture_cudagraph(self):
+        if not _is_cuda(self):
+            return orig["capture_cudagraph"](self)
+        config = self.config
+        hf_config = config.hf_config
+        g = _glue(self)
+        max_bs = min(config.max_num_seqs, 512)
+        outputs = torch.zeros(max_bs, hf_config.hidden_size)
+        self.graph_bs = [1, 2, 4, 8] + list(range(16, max_bs + 1, 16))
+        self.graphs = {}
+        self.graph_pool = None
+        g.dev.zero_()
+        for bs in reversed(self.graph_bs):
+            ids, pos, slots, lens, tab = g.graph_buffers(bs)
+            graph = torch.cuda.CUDAGraph()
+            set_context(False, slot_mapping=slots, context_lens=lens, block_tables=tab)
+            outputs[:bs] = self.model(ids, pos)            # warm-up outside capture
+            with torch.cuda.graph(graph, self.graph_pool):
+                outputs[:bs] = self.model(ids, pos)
+            if self.graph_pool is None:
+                self.graph_pool = graph.pool()
+            self.graphs[bs] = graph
+            torch.cuda.synchronize()
+            reset_context()
+        g.graph_bs = list(self.graph_bs)
+        self.graph_vars = dict(outputs=outputs, staging=g.dev)
+
+    for name, fn in (("prepare_block_tables", prepare_block_tables), ("prepare_prefill", prepare_prefill),
+                     ("prepare_decode", prepare_decode), ("run_model", run_model),
+                     ("capture_cudagraph", capture_cudagraph)):
+        setattr(model_runner_cls, name, fn)

@@ -1,0 +1,139 @@
+"""Seeded synthetic inputs shared by the golden generator, the CPU tests and the GPU parity tests.
+
+Inputs are regenerated from seeds (fixtures stay small); every fixture stores a sha256 of the
+regenerated inputs so an RNG change shows up as "fixture inputs differ", not as a parity failure.
+"""
+from __future__ import annotations
+
+import hashlib
+
+import torch
+
+
+def sha(*tensors) -> str:
+    h = hashlib.sha256()
+    for t in tensors:
+        if t is None:
+            continue
+        t = t.contiguous()
+        if t.dtype == torch.bfloat16:
+            t = t.view(torch.int16)
+        h.update(t.numpy().tobytes())
+    return h.hexdigest()
+
+
+def bf16_bits(t: torch.Tensor):
+    return t.contiguous().view(torch.int16).numpy()
+
+
+def from_bits(a) -> torch.Tensor:
+    return torch.from_numpy(a.copy()).view(torch.bfloat16)
+
+
+# name -> (seed, ctx lens, Hq, Hkv, num_blocks, block_size)
+DECODE_CASES = {
+    # BASELINE.json configs[0]: bs=1, ctx=512, 16 q / 8 kv heads, head_dim 128, block 256
+    "c1_bs1_ctx512": (0, [512], 16, 8, 4, 256),
+    "ragged_g4": (1, [1, 255, 700, 256, 257], 8, 2, 12, 256),
+    "ragged_g2_tail": (2, [17, 513, 31, 300], 4, 2, 10, 256),
+    "g1_single_head": (3, [129, 64], 2, 2, 4, 256),
+    "g8": (4, [333, 16], 8, 1, 6, 256),
+}
+
+# name -> (seed, lens, Hq, Hkv)   (no prefix: Lq == Lk)
+PREFILL_CASES = {
+    "p_small": (10, [5, 64, 130], 4, 2),
+    "p_tiles": (11, [63, 65, 128, 1], 4, 1),
+    "p_qwen06_heads": (12, [200], 16, 8),
+}
+
+# name -> (seed, [(cached, new)], Hq, Hkv, num_blocks)   prefix-cache prefill from the paged cache
+PREFIX_CASES = {
+    "px_shared512": (20, [(0, 300), (512, 300), (256, 70)], 4, 2, 16),
+    "px_one_token": (21, [(256, 1), (512, 64)], 8, 2, 12),
+    "px_g4_long": (22, [(768, 129)], 8, 2, 8),
+}
+
+D = 128
+
+
+def make_decode_case(name: str):
+    seed, lens, hq, hkv, nblk, bsz = DECODE_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    bs = len(lens)
+    q = torch.randn(bs, hq, D, generator=g).to(torch.bfloat16)
+    k_cache = torch.randn(nblk, bsz, hkv, D, generator=g).to(torch.bfloat16)
+    v_cache = torch.randn(nblk, bsz, hkv, D, generator=g).to(torch.bfloat16)
+    need = [(c + bsz - 1) // bsz for c in lens]
+    width = max(need)
+    perm = torch.randperm(nblk, generator=g).tolist()
+    assert sum(need) <= nblk
+    tables = torch.full((bs, width), -1, dtype=torch.int32)
+    pos = 0
+    for b, n in enumerate(need):
+        for j in range(n):
+            tables[b, j] = perm[pos]
+            pos += 1
+    ctx = torch.tensor(lens, dtype=torch.int32)
+    return dict(q=q, k_cache=k_cache, v_cache=v_cache, context_lens=ctx, block_tables=tables,
+                scale=D ** -0.5, hq=hq, hkv=hkv, block_size=bsz)
+
+
+def make_prefill_case(name: str):
+    seed, lens, hq, hkv = PREFILL_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    total = sum(lens)
+    q = torch.randn(total, hq, D, generator=g).to(torch.bfloat16)
+    k = torch.randn(total, hkv, D, generator=g).to(torch.bfloat16)
+    v = torch.randn(total, hkv, D, generator=g).to(torch.bfloat16)
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32)
+    return dict(q=q, k=k, v=v, cu_seqlens_q=cu, cu_seqlens_k=cu.clone(), max_seqlen_q=max(lens),
+                max_seqlen_k=max(lens), scale=D ** -0.5, hq=hq, hkv=hkv)
+
+
+def make_prefix_case(name: str, block_size: int = 256):
+    """Prefill with cached prefixes: all keys (cached + new) already sit in the paged cache."""
+    seed, pairs, hq, hkv, nblk = PREFIX_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    lq = [n for _, n in pairs]
+    lk = [c + n for c, n in pairs]
+    q = torch.randn(sum(lq), hq, D, generator=g).to(torch.bfloat16)
+    k_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
+    v_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
+    need = [(c + block_size - 1) // block_size for c in lk]
+    assert sum(need) <= nblk
+    perm = torch.randperm(nblk, generator=g).tolist()
+    tables = torch.full((len(pairs), max(need)), -1, dtype=torch.int32)
+    pos = 0
+    for b, n in enumerate(need):
+        for j in range(n):
+            tables[b, j] = perm[pos]
+            pos += 1
+    cu_q = torch.tensor([0] + list(torch.tensor(lq).cumsum(0)), dtype=torch.int32)
+    cu_k = torch.tensor([0] + list(torch.tensor(lk).cumsum(0)), dtype=torch.int32)
+    return dict(q=q, k_cache=k_cache, v_cache=v_cache, cu_seqlens_q=cu_q, cu_seqlens_k=cu_k,
+                max_seqlen_q=max(lq), max_seqlen_k=max(lk), block_tables=tables, scale=D ** -0.5,
+                hq=hq, hkv=hkv, block_size=block_size)
+
+
+def make_store_case(seed: int, n: int, hkv: int, nblk: int, block_size: int = 256, strided_v: bool = True,
+                    dup_slot0: int = 0, neg: int = 0):
+    """Store inputs shaped like the model's: K contiguous, V a strided view of a fused qkv row."""
+    g = torch.Generator().manual_seed(seed)
+    row = hkv * D
+    key = torch.randn(n, hkv, D, generator=g).to(torch.bfloat16)
+    if strided_v:
+        fused = torch.randn(n, 3 * row, generator=g).to(torch.bfloat16)
+        value = fused[:, 2 * row:].view(n, hkv, D)
+    else:
+        value = torch.randn(n, hkv, D, generator=g).to(torch.bfloat16)
+    slots = torch.randperm(nblk * block_size, generator=g)[:n].to(torch.int32)
+    if dup_slot0:  # zero-padded graph rows: slot 0 repeated with identical data (model_runner.py:291-293)
+        slots[-dup_slot0:] = 0
+        key[-dup_slot0:] = key[-1]
+        value[-dup_slot0:] = value[-1]
+    if neg:
+        slots[:neg] = -1
+    k_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
+    v_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
+    return dict(key=key, value=value, slot_mapping=slots, k_cache=k_cache, v_cache=v_cache)
