@@ -52,7 +52,7 @@ def test_store_bit_exact_vs_oracle(ops, n, hkv, dup, neg, strided):
         fused = torch.zeros(n, 3 * row, dtype=torch.bfloat16, device=DEV)
         fused[:, 2 * row:] = c["value"].reshape(n, row).to(DEV)
         g["value"] = fused[:, 2 * row:].view(n, hkv, 128)
-        assert g["value"].stride(0) == 3 * row
+        assert n == 1 or g["value"].stride(0) == 3 * row
     ops.store_kvcache(g["key"], g["value"], g["k_cache"], g["v_cache"], g["slot_mapping"])
     torch.cuda.synchronize()
     assert torch.equal(g["k_cache"].cpu().view(torch.int16), kc.view(torch.int16))

@@ -1,0 +1,90 @@
+"""Materialise the reference-side binding of INTEGRATION.md on a COPY of the installed reference.
+
+    python tools/make_integration.py [--src baseline/_ref] [--dst build/nanovllm_cuda]
+
+Copies `<src>/nanovllm` to `<dst>/nanovllm` (git-ignored, never committed) and applies exactly the
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4), plus two environment-compat
+edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
+to construct under this image's transformers 5.5 and network setup.  Every edit is an
+anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
+touched, so running the copy with `attn_backend="flash"` is the reference's stock path.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import shutil
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+EDITS = [
+    # ---- A1: admit the backend name (nanovllm/config.py:6)
+    ("nanovllm/config.py",
+     'VALID_ATTN_BACKENDS = ("flash", "sdpa", "sdpa.math", "triton")',
+     'VALID_ATTN_BACKENDS = ("flash", "sdpa", "sdpa.math", "triton", "cuda")'),
+    # ---- A2: string -> class dispatch (nanovllm/models/qwen3.py:52-56)
+    ("nanovllm/models/qwen3.py",
+     '        else:\n            raise ValueError(f"Unknown attention backend: {attn_backend}")',
+     '        elif attn_backend == "cuda":\n'
+     '            from nanovllm.layers.attention_cuda import Attention\n'
+     '            attn_kwargs = {"block_size": block_size}\n'
+     '        else:\n            raise ValueError(f"Unknown attention backend: {attn_backend}")'),
+    # ---- A4: runner glue (prepare_* / capture / replay) for the cuda backend, appended to model_runner.py
+    ("nanovllm/engine/model_runner.py", None,
+     '\n\n# --- cuda attention backend: B200-native prepare/capture glue (other backends keep the methods above)\n'
+     'from nano_vllm_learn_b200.runner_glue import install as _install_cuda_glue\n'
+     '_install_cuda_glue(ModelRunner, set_context, get_context, reset_context)\n'),
+    # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
+    ("nanovllm/config.py",
+     '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',
+     '        self.hf_config = AutoConfig.from_pretrained(self.model)\n'
+     '        _rs = getattr(self.hf_config, "rope_scaling", None)\n'
+     '        if isinstance(_rs, dict) and _rs.get("rope_type", _rs.get("type", "default")) == "default":\n'
+     '            self.hf_config.rope_scaling = None   # compat: get_rope() asserts None and lru_caches its args\n'),
+    # ---- C2: "localhost" may not resolve inside the GPU box; allow a port override for back-to-back engines
+    ("nanovllm/engine/model_runner.py",
+     'dist.init_process_group("nccl", "tcp://localhost:2333", world_size=self.world_size, rank=rank)',
+     'dist.init_process_group("nccl", "tcp://127.0.0.1:" + __import__("os").environ.get("NVLLM_PORT", "2333"), '
+     'world_size=self.world_size, rank=rank)'),
+]
+
+# ---- A3: the backend module the dispatch imports (new file nanovllm/layers/attention_cuda.py)
+ATTENTION_CUDA = '''"""cuda attention backend: hand-written sm_100a kernels behind the C ABI of nvllm_attn.h."""
+from nano_vllm_learn_b200.attention_cuda import Attention, bind_context
+from nanovllm.utils.context import get_context
+
+bind_context(get_context)
+
+__all__ = ["Attention"]
+'''
+
+
+def make(src: str, dst: str) -> str:
+    src_pkg = os.path.join(src, "nanovllm")
+    if not os.path.isdir(src_pkg):
+        raise SystemExit(f"{src_pkg} not found (pip --target install of the reference, see DESIGN.md)")
+    if os.path.isdir(dst):
+        shutil.rmtree(dst)
+    os.makedirs(dst)
+    shutil.copytree(src_pkg, os.path.join(dst, "nanovllm"), ignore=shutil.ignore_patterns("__pycache__"))
+    for rel, old, new in EDITS:
+        path = os.path.join(dst, rel)
+        text = open(path).read()
+        if old is None:
+            text = text + new
+        else:
+            if text.count(old) != 1:
+                raise SystemExit(f"anchor for {rel} matched {text.count(old)} times: {old[:60]!r}")
+            text = text.replace(old, new)
+        open(path, "w").write(text)
+    with open(os.path.join(dst, "nanovllm", "layers", "attention_cuda.py"), "w") as f:
+        f.write(ATTENTION_CUDA)
+    return dst
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--src", default=os.path.join(ROOT, "baseline", "_ref"))
+    ap.add_argument("--dst", default=os.path.join(ROOT, "build", "nanovllm_cuda"))
+    a = ap.parse_args()
+    print(make(a.src, a.dst))

@@ -1,0 +1,105 @@
+"""Decode-kernel tuning sweep on one GPU: variants x split counts x shapes, CUDA-event timed with an
+L2 flush between launches.  Prints one JSON line per point (collected under gpurun_out/)."""
+import argparse
+import json
+import os
+import statistics
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from nano_vllm_learn_b200 import _lib, ops  # noqa: E402
+
+D, BLOCK = 128, 256
+
+
+def make(bs, ctx, hq, hkv, dev, width=None, seed=0):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    pages = (ctx + BLOCK - 1) // BLOCK
+    nblk = bs * pages
+    kc = torch.empty(nblk, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+    vc = torch.empty(nblk, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+    q = torch.empty(bs, hq, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+    tab = torch.randperm(nblk, generator=g, device=dev).to(torch.int32).view(bs, pages)
+    if width and width > pages:
+        wide = torch.zeros(bs, width, dtype=torch.int32, device=dev)
+        wide[:, :pages] = tab
+        tab = wide
+    lens = torch.full((bs,), ctx, dtype=torch.int32, device=dev)
+    nbytes = bs * ctx * hkv * D * 4 + 2 * bs * hq * D * 2 + 4 * bs + 4 * bs * pages
+    return q, kc, vc, lens, tab, nbytes
+
+
+def timeit(fn, flush, iters=12):
+    for _ in range(3):
+        fn()
+    ts = []
+    for _ in range(iters):
+        flush.zero_()
+        a = torch.cuda.Event(enable_timing=True)
+        b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e3)
+    return statistics.median(ts), min(ts)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shapes", default="c2")
+    ap.add_argument("--variants", default="all")
+    ap.add_argument("--flash", action="store_true", help="also time flash-attn's kernel on the same inputs")
+    args = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    lib = _lib.load()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    shapes = {
+        # name: (bs, ctx, hq, hkv, table width or None, split list)
+        "c1": [(1, 512, 16, 8, 16, [0, 1, 2, 4, 8])],
+        "c2": [(bs, ctx, 16, 8, 16, [0, 1, 2, 4, 8, 16]) for bs in (16, 32, 64) for ctx in (1024, 2048, 4096)],
+        "c4": [(128, 4096, 32 // tp, 8 // tp, 16, [0, 1, 2, 4, 8]) for tp in (1, 2, 4, 8)],
+        "c5": [(bs, 32768, 32 // tp, 8 // tp, 160, [0, 8, 16, 32, 64]) for bs in (1, 4) for tp in (1, 8)],
+    }
+    sel = []
+    for s in args.shapes.split(","):
+        sel += shapes[s]
+    nvar = lib.nvllm_paged_decode_num_variants()
+    variants = list(range(nvar)) if args.variants == "all" else [int(v) for v in args.variants.split(",")]
+    fa = None
+    if args.flash:
+        try:
+            from flash_attn import flash_attn_with_kvcache as fa
+        except Exception as e:
+            print(json.dumps({"flash": f"unavailable: {e}"}))
+    for bs, ctx, hq, hkv, width, split_list in sel:
+        q, kc, vc, lens, tab, nbytes = make(bs, ctx, hq, hkv, dev, width)
+        out = torch.empty_like(q)
+        if fa is not None:
+            f = lambda: fa(q.unsqueeze(1), kc, vc, cache_seqlens=lens, block_table=tab, softmax_scale=D ** -0.5, causal=True)
+            med, mn = timeit(f, flush)
+            print(json.dumps(dict(impl="flash", bs=bs, ctx=ctx, hq=hq, hkv=hkv, us=round(med, 2), us_min=round(mn, 2),
+                                  gbs=round(nbytes / med / 1e3, 1))), flush=True)
+        for v in variants:
+            lib.nvllm_paged_decode_set_variant(v)
+            for s in split_list:
+                ns = s if s > 0 else ops.plan_num_splits(bs, hkv, tab.size(1) * BLOCK)
+                if ctx // ns < 32:
+                    continue
+                ws = torch.empty(max(ops.decode_workspace_bytes(bs, hq, D, ns), 16), dtype=torch.uint8, device=dev)
+                f = lambda: ops.flash_attn_with_kvcache(q, kc, vc, lens, tab, softmax_scale=D ** -0.5, num_splits=ns,
+                                                        out=out, workspace=ws)
+                med, mn = timeit(f, flush)
+                print(json.dumps(dict(impl="cuda", variant=v, bs=bs, ctx=ctx, hq=hq, hkv=hkv, splits=ns,
+                                      planned=(s == 0), us=round(med, 2), us_min=round(mn, 2),
+                                      gbs=round(nbytes / med / 1e3, 1))), flush=True)
+        del q, kc, vc
+        torch.cuda.empty_cache()
+    lib.nvllm_paged_decode_set_variant(-1)
+
+
+if __name__ == "__main__":
+    main()
