@@ -36,7 +36,7 @@ class _Slot:
     """One pinned staging slot + its typed numpy view and the event that guards reuse."""
 
     def __init__(self, nbytes: int, pinned: bool):
-        self.host = torch.empty(nbytes, dtype=torch.uint8, pin_memory=pinned)
+        self.host = torch.empty(nbytes, dtype=torch.uint8, device="cpu", pin_memory=pinned)
         self.np = self.host.numpy()
         self.event = torch.cuda.Event() if pinned else None
 
