@@ -117,7 +117,7 @@ NVLLM_API int nvllm_store_kvcache(const void* key, int64_t key_row_stride,
  *   share of the LIVE ctx_b (not of the table width).  num_splits > 1 needs a
  *   workspace of nvllm_paged_decode_workspace_bytes(); the combine pass is
  *   launched by this call.
- *   Supported: head_dim == 128, G in {1,2,4,8}, block_size % 16 == 0.
+ *   Supported: head_dim == 128, G in {1,2,4,8}, block_size % 32 == 0.
  * ---------------------------------------------------------------------- */
 NVLLM_API int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride,
                        const void* k_cache, const void* v_cache,
@@ -164,6 +164,8 @@ NVLLM_API int32_t nvllm_paged_decode_num_variants(void);
  *       block_tables[i * table_stride + t / block_size].
  *   q   [sum Lq, num_q_heads, head_dim] with row stride q_row_stride
  *   out [sum Lq, num_q_heads, head_dim] contiguous
+ *   total_q = rows of q/out; total_k = rows of dense k/v, or
+ *   num_blocks * block_size for the paged caches (TMA bounds).
  *   max_seqlen_q bounds the grid (as in the reference call).
  *   Supported: head_dim == 128, num_q_heads % num_kv_heads == 0.
  * ---------------------------------------------------------------------- */
@@ -173,16 +175,21 @@ NVLLM_API int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_strid
                          int64_t cache_block_stride,
                          const int32_t* cu_seqlens_q,
                          const int32_t* cu_seqlens_k,
-                         int32_t batch, int32_t max_seqlen_q,
-                         int32_t max_seqlen_k,
+                         int32_t batch, int32_t total_q, int32_t total_k,
+                         int32_t max_seqlen_q, int32_t max_seqlen_k,
                          const int32_t* block_tables, int64_t table_stride,
                          int32_t num_q_heads, int32_t num_kv_heads,
                          int32_t head_dim, int32_t block_size, float scale,
                          void* stream);
 
-/* Tuning hook: 0 = mma.sync path, 1 = tcgen05/TMEM path (when built),
- * -1 = default. */
+/* Tuning hook: 0 = mma.sync tile kernel, 1 = tcgen05/TMEM tile kernel,
+ * -1 = default (tcgen05). */
 NVLLM_API int nvllm_varlen_prefill_set_variant(int32_t variant);
+
+/* Debug hook: when non-NULL, CTA (q-tile 0, head 0, sequence 0) of the tcgen05
+ * kernel dumps its first raw S tile (128x128 fp32) followed by its first raw
+ * O partial (128x128 fp32) to this device buffer (>= 131072 bytes). */
+NVLLM_API void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr);
 
 /* ------------------------------------------------------------------------
  * (4) runner glue index math on the HOST (plain C, no CUDA): the integer

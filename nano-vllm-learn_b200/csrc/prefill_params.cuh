@@ -1,0 +1,34 @@
+// Parameters shared by the two varlen-prefill kernels (mma.sync tiles and tcgen05/TMEM tiles).
+#pragma once
+
+#include "common.cuh"
+
+namespace nvllm {
+
+struct PrefillParams {
+  const __nv_bfloat16* q;
+  int64_t q_row_stride;
+  const __nv_bfloat16* k;
+  const __nv_bfloat16* v;
+  int64_t k_row_stride;  // dense: row stride; paged: token stride
+  int64_t v_row_stride;
+  int64_t block_stride;  // paged only
+  const int32_t* cu_q;
+  const int32_t* cu_k;
+  const int32_t* block_tables;  // nullptr -> dense k/v
+  int64_t table_stride;
+  __nv_bfloat16* out;
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t group;
+  int32_t block_size;
+  int32_t total_q;  // rows of q / out
+  int32_t total_k;  // dense: rows of k/v; paged: num_blocks * block_size
+  float scale_log2;
+};
+
+// prefill_tcgen05.cu: returns NVLLM_OK and sets *handled when it launched the tcgen05 kernel.
+int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, int max_seqlen_k,
+                           cudaStream_t stream, bool* handled);
+
+}  // namespace nvllm

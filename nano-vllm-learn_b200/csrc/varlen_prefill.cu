@@ -10,31 +10,9 @@
 // the paged cache via block_tables.  The tcgen05/TMEM kernel in prefill_tcgen05.cu supersedes it for
 // full tiles when enabled (nvllm_varlen_prefill_set_variant).
 #include "common.cuh"
+#include "prefill_params.cuh"
 
 namespace nvllm {
-
-struct PrefillParams {
-  const __nv_bfloat16* q;
-  int64_t q_row_stride;
-  const __nv_bfloat16* k;
-  const __nv_bfloat16* v;
-  int64_t k_row_stride;  // dense: row stride; paged: token stride
-  int64_t v_row_stride;
-  int64_t block_stride;  // paged only
-  const int32_t* cu_q;
-  const int32_t* cu_k;
-  const int32_t* block_tables;  // nullptr -> dense k/v
-  int64_t table_stride;
-  __nv_bfloat16* out;
-  int32_t num_q_heads;
-  int32_t group;
-  int32_t block_size;
-  float scale_log2;
-};
-
-// defined in prefill_tcgen05.cu
-int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, int max_seqlen_k,
-                           cudaStream_t stream, bool* handled);
 
 constexpr int kBM = 64;  // query rows per CTA
 constexpr int kBN = 64;  // keys per tile
@@ -272,11 +250,13 @@ int nvllm_varlen_prefill_set_variant(int32_t variant) {
 int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
                          const void* v, int64_t v_row_stride, int64_t cache_block_stride,
                          const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k, int32_t batch,
-                         int32_t max_seqlen_q, int32_t max_seqlen_k, const int32_t* block_tables,
+                         int32_t total_q, int32_t total_k, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                         const int32_t* block_tables,
                          int64_t table_stride, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                          int32_t block_size, float scale, void* stream) {
   using namespace nvllm;
-  if (batch < 0 || max_seqlen_q < 0 || max_seqlen_k < 0 || num_q_heads <= 0 || num_kv_heads <= 0)
+  if (batch < 0 || max_seqlen_q < 0 || max_seqlen_k < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || total_q < 0 ||
+      total_k < 0)
     return NVLLM_ERR_BAD_ARG;
   if (batch == 0 || max_seqlen_q == 0) return NVLLM_OK;
   if (!out || !q || !k || !v || !cu_seqlens_q || !cu_seqlens_k) return NVLLM_ERR_BAD_ARG;
@@ -301,8 +281,11 @@ int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride, const v
   p.table_stride = table_stride;
   p.out = static_cast<__nv_bfloat16*>(out);
   p.num_q_heads = num_q_heads;
+  p.num_kv_heads = num_kv_heads;
   p.group = num_q_heads / num_kv_heads;
   p.block_size = block_size > 0 ? block_size : 256;
+  p.total_q = total_q;
+  p.total_k = total_k;
   p.scale_log2 = scale * kLog2e;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);

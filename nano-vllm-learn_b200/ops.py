@@ -35,6 +35,15 @@ def reset_launch_count() -> None:
     _lib.load().nvllm_reset_launch_count()
 
 
+def set_prefill_variant(variant: int) -> None:
+    """0 = mma.sync tile kernel, 1 = tcgen05/TMEM tile kernel, -1 = library default."""
+    _lib.check(_lib.load().nvllm_varlen_prefill_set_variant(variant), "set_prefill_variant")
+
+
+def set_decode_variant(variant: int) -> None:
+    _lib.check(_lib.load().nvllm_paged_decode_set_variant(variant), "set_decode_variant")
+
+
 def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                   slot_mapping: torch.Tensor) -> None:
     """key/value [N, Hkv, D] (arbitrary row stride) -> k_cache/v_cache [num_blocks, block, Hkv, D]."""
@@ -149,16 +158,19 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         _, block_size, num_kv_heads, _ = k.shape
         assert k.stride(-1) == 1 and k.stride(2) == head_dim
         k_row, v_row, blk = k.stride(1), v.stride(1), k.stride(0)
+        assert blk == block_size * k_row, "paged cache must be one [num_blocks * block_size, Hkv * D] matrix"
+        total_k = k.shape[0] * block_size
         bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
     else:
         assert k.dim() == 3 and v.dim() == 3
         num_kv_heads = k.shape[1]
         assert k.stride(-1) == 1 and k.stride(1) == head_dim and v.stride(-1) == 1 and v.stride(1) == head_dim
         k_row, v_row, blk = k.stride(0), v.stride(0), 0
+        total_k = k.shape[0]
         block_size, bt_ptr, bt_stride = 0, 0, 0
     st = lib.nvllm_varlen_prefill(out.data_ptr(), q.data_ptr(), q.stride(0), k.data_ptr(), k_row, v.data_ptr(), v_row,
-                                  blk, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), batch, int(max_seqlen_q),
-                                  int(max_seqlen_k), bt_ptr, bt_stride, num_q_heads, num_kv_heads, head_dim,
+                                  blk, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), batch, total_q, total_k,
+                                  int(max_seqlen_q), int(max_seqlen_k), bt_ptr, bt_stride, num_q_heads, num_kv_heads, head_dim,
                                   block_size, float(softmax_scale), _stream())
     _lib.check(st, "varlen_prefill")
     return out

@@ -1,0 +1,92 @@
+"""GPU: the tcgen05/TMEM prefill kernel (variant 1) against the oracle, the reference fixtures and the
+mma.sync tile kernel on the same inputs."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+from oracle import paged_attention_oracle as orc
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+DEV = "cuda"
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture()
+def ops(lib):
+    from nano_vllm_learn_b200 import ops as _ops
+    _ops.set_prefill_variant(1)
+    yield _ops
+    _ops.set_prefill_variant(-1)
+
+
+def _cuda(c):
+    return {k: (v.to(DEV) if isinstance(v, torch.Tensor) else v) for k, v in c.items()}
+
+
+def _maxerr(a, b):
+    return (a.float().cpu() - b.float().cpu()).abs().max().item()
+
+
+@pytest.mark.parametrize("name", list(cases.PREFILL_CASES))
+def test_tcgen05_prefill_vs_oracle_and_fixture(ops, name):
+    c = cases.make_prefill_case(name)
+    want = orc.varlen_prefill_ref(c["q"], c["k"], c["v"], c["cu_seqlens_q"], c["cu_seqlens_k"], c["scale"])
+    g = _cuda(c)
+    got = ops.flash_attn_varlen_func(g["q"], g["k"], g["v"], c["max_seqlen_q"], g["cu_seqlens_q"], c["max_seqlen_k"],
+                                     g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True)
+    assert _maxerr(got, want) <= TOL
+    gold = cases.from_bits(np.load(os.path.join(GOLD, f"prefill_{name}.npz"))["out"])
+    assert _maxerr(got, gold) <= TOL
+
+
+@pytest.mark.parametrize("name", list(cases.PREFIX_CASES))
+def test_tcgen05_prefix_prefill_vs_oracle(ops, name):
+    c = cases.make_prefix_case(name)
+    want = orc.varlen_prefill_ref(c["q"], c["k_cache"], c["v_cache"], c["cu_seqlens_q"], c["cu_seqlens_k"], c["scale"],
+                                  c["block_tables"])
+    g = _cuda(c)
+    got = ops.flash_attn_varlen_func(g["q"], g["k_cache"], g["v_cache"], c["max_seqlen_q"], g["cu_seqlens_q"],
+                                     c["max_seqlen_k"], g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True,
+                                     block_table=g["block_tables"])
+    assert _maxerr(got, want) <= TOL
+
+
+def test_tcgen05_full_size_vs_mma_kernel(ops):
+    """bench.py's prefill step (16 x 1024, 16q/8kv) with strided k/v views: both kernels agree; one
+    sequence against the CPU oracle."""
+    bsz, L, hq, hkv = 16, 1024, 16, 8
+    g = torch.Generator(device=DEV).manual_seed(9)
+    total = bsz * L
+    q = torch.randn(total, hq, 128, generator=g, device=DEV, dtype=torch.float32).to(torch.bfloat16)
+    fused = torch.randn(total, 2 * hkv * 128, generator=g, device=DEV, dtype=torch.float32).to(torch.bfloat16)
+    k = fused[:, :hkv * 128].view(total, hkv, 128)
+    v = fused[:, hkv * 128:].view(total, hkv, 128)
+    cu = torch.arange(0, total + 1, L, dtype=torch.int32, device=DEV)
+    scale = 128 ** -0.5
+    out = ops.flash_attn_varlen_func(q, k, v, L, cu, L, cu, softmax_scale=scale, causal=True)
+    ops.set_prefill_variant(0)
+    ref = ops.flash_attn_varlen_func(q, k, v, L, cu, L, cu, softmax_scale=scale, causal=True)
+    ops.set_prefill_variant(1)
+    assert _maxerr(out, ref) <= 8e-3
+    i = 11
+    want = orc.varlen_prefill_ref(q[i * L:(i + 1) * L].cpu(), k[i * L:(i + 1) * L].cpu(), v[i * L:(i + 1) * L].cpu(),
+                                  torch.tensor([0, L], dtype=torch.int32), torch.tensor([0, L], dtype=torch.int32), scale)
+    assert _maxerr(out[i * L:(i + 1) * L], want) <= TOL
+
+
+def test_tcgen05_ragged_batch_vs_mma_kernel(ops):
+    lens = [1, 127, 128, 129, 255, 257, 700, 33]
+    hq, hkv = 8, 2
+    g = torch.Generator(device=DEV).manual_seed(4)
+    total = sum(lens)
+    q = torch.randn(total, hq, 128, generator=g, device=DEV, dtype=torch.float32).to(torch.bfloat16)
+    k = torch.randn(total, hkv, 128, generator=g, device=DEV, dtype=torch.float32).to(torch.bfloat16)
+    v = torch.randn(total, hkv, 128, generator=g, device=DEV, dtype=torch.float32).to(torch.bfloat16)
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32, device=DEV)
+    out = ops.flash_attn_varlen_func(q, k, v, max(lens), cu, max(lens), cu, softmax_scale=128 ** -0.5)
+    want = orc.varlen_prefill_ref(q.cpu(), k.cpu(), v.cpu(), cu.cpu(), cu.cpu(), 128 ** -0.5)
+    assert _maxerr(out, want) <= TOL
