@@ -5,10 +5,10 @@
 //
 // Tensor-core bound: FLOPs = 4 * Hq * 128 * sum_i [Lq_i * cached_i + Lq_i (Lq_i + 1) / 2].
 //
-// This file holds the warp-level (mma.sync m16n8k16) tile kernel: 64 query rows x 64 keys per step,
-// four warps of 16 rows, K/V tiles double-buffered with cp.async from either this step's dense k/v or
-// the paged cache via block_tables.  The tcgen05/TMEM kernel in prefill_tcgen05.cu supersedes it for
-// full tiles when enabled (nvllm_varlen_prefill_set_variant).
+// This file holds the C-ABI entry point and the warp-level (mma.sync m16n8k16) tile kernel: 64 query rows x
+// 64 keys per step, four warps of 16 rows, K/V tiles double-buffered with cp.async.  The default path is the
+// tcgen05/TMEM kernel in prefill_tcgen05.cu; this kernel stays as the cross-check (variant 0) and as the
+// path taken when no TMA bounds are given or the driver cannot encode tensor maps.
 #include "common.cuh"
 #include "prefill_params.cuh"
 
@@ -289,7 +289,7 @@ int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride, const v
   p.scale_log2 = scale * kLog2e;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (g_prefill_variant == 1) {
+  if (g_prefill_variant != 0) {  // default (-1) and 1: tcgen05/TMEM kernel; 0 forces the mma.sync tile kernel
     bool handled = false;
     int rc = launch_prefill_tcgen05(p, batch, max_seqlen_q, max_seqlen_k, st, &handled);
     if (rc != NVLLM_OK || handled) return rc;
