@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-tp", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true")
     ap.add_argument("--cpu-sample-bs", type=int, default=2)
     return ap.parse_args()
 
@@ -274,6 +275,10 @@ def run_cuda(args):
         torch.cuda.empty_cache()
         tp_strong = run_tp_point(args, dev, world, rank, ops, dist)
 
+    prefill = None
+    if rank == 0 and not args.no_prefill:
+        prefill = run_prefill_points(dev, ops)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, sample_bs=args.cpu_sample_bs, iters=None)
@@ -293,7 +298,7 @@ def run_cuda(args):
                                  (wl.layers * wl.bs * ((args.ctx + BLOCK - 1) // BLOCK) * BLOCK * wl.hkv * D * 4 / 1e9),
                            "timing": "CUDA events on the launch stream, max over ranks"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
-                "cpu_baseline": cpu, "tp_strong": tp_strong}
+                "cpu_baseline": cpu, "tp_strong": tp_strong, "prefill": prefill}
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -358,13 +363,12 @@ def run_tp_point(args, dev, world, rank, ops, dist):
     """configs[3]: Qwen3-8B-shape decode, bs=128 ctx=4096, 32q/8kv heads split `world` ways (strong scaling)."""
     if 8 % world != 0:
         return None
-    hq, hkv, bs, ctx, layers = 32 // world, 8 // world, 128, 4096, 2
+    hq, hkv, bs, ctx, layers = 32 // world, 8 // world, 128, 4096, 4
     wl = Workload(dev, layers, bs, ctx, hq, hkv, seed=100 + rank)
     scale = D ** -0.5
     splits = ops.plan_num_splits(bs, hkv, wl.tables.size(1) * BLOCK)
     out = torch.empty(bs, hq, D, dtype=torch.bfloat16, device=dev)
     ws = torch.empty(max(ops.decode_workspace_bytes(bs, hq, D, splits), 16), dtype=torch.uint8, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > L2: shards shrink to 268 MB/layer at tp=8
 
     def one(l):
         ops.flash_attn_with_kvcache(wl.q[l].view(bs, hq, D), wl.kv[0, l], wl.kv[1, l], wl.lens, wl.tables,
@@ -373,8 +377,7 @@ def run_tp_point(args, dev, world, rank, ops, dist):
     for _ in range(3):
         one(0)
     times = []
-    for i in range(10):
-        flush.zero_()
+    for i in range(12):   # rotate over 4 distinct caches (>= 1.07 GB in total even at tp=8): nothing is re-read from L2
         a = torch.cuda.Event(enable_timing=True)
         b = torch.cuda.Event(enable_timing=True)
         a.record()
@@ -392,7 +395,54 @@ def run_tp_point(args, dev, world, rank, ops, dist):
     return {"workload": f"Qwen3-8B-shape decode op, bs=128 ctx=4096, tp={world}: {hq}q/{hkv}kv heads per GPU",
             "us_per_launch_max_over_ranks": round(us, 2), "per_gpu_GBps": round(gbs, 1),
             "aggregate_GBps": round(gbs * world, 1), "frac_of_measured_peak": round(gbs / peak, 4),
-            "num_splits": splits, "l2": "256 MB flush write between timed launches"}
+            "num_splits": splits, "l2": "launches rotate over 4 distinct caches, working set >> 126 MB L2"}
+
+
+def run_prefill_points(dev, ops):
+    """Secondary line: the tcgen05 varlen-prefill kernel against the tensor roofline.
+    FLOPs = 4*Hq*128*sum_i[Lq_i*cached_i + Lq_i(Lq_i+1)/2]; peak = measured bf16 burst."""
+    peak = 1590.0
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            peak = float(json.load(f)["bf16_tflops"])
+    out = []
+    for name, b, lq, cached, hq, hkv in (("bench.py prefill step: 16 x 1024, 16q/8kv", 16, 1024, 0, 16, 8),
+                                         ("prefix cache: 16 x (512 new + 512 cached), 16q/8kv", 16, 512, 512, 16, 8),
+                                         ("Qwen3-8B-shape: 4 x 4096, 32q/8kv", 4, 4096, 0, 32, 8)):
+        g = torch.Generator(device=dev).manual_seed(1)
+        lk = lq + cached
+        q = torch.empty(b * lq, hq, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+        cu_q = torch.arange(0, b * lq + 1, lq, dtype=torch.int32, device=dev)
+        cu_k = torch.arange(0, b * lk + 1, lk, dtype=torch.int32, device=dev)
+        if cached:
+            pages = (lk + BLOCK - 1) // BLOCK
+            k = torch.empty(b * pages, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+            v = torch.empty(b * pages, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+            tab = torch.randperm(b * pages, generator=g, device=dev).to(torch.int32).view(b, pages)
+        else:
+            k = torch.empty(b * lk, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+            v = torch.empty(b * lk, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+            tab = None
+        o = torch.empty_like(q)
+        fl = 4 * hq * D * b * (lq * cached + lq * (lq + 1) // 2)
+        fn = lambda: ops.flash_attn_varlen_func(q, k, v, lq, cu_q, lk, cu_k, softmax_scale=D ** -0.5, block_table=tab, out=o)
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(10):
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            fn()
+            b_.record()
+            torch.cuda.synchronize()
+            ts.append(a_.elapsed_time(b_))
+        us = statistics.median(ts) * 1e3
+        out.append({"workload": name, "kernel": "prefill_tcgen05_kernel", "us": round(us, 1),
+                    "achieved": round(fl / us / 1e6, 1), "peak": peak, "unit": "TFLOP/s", "bound": "tensor",
+                    "frac": round(fl / us / 1e6 / peak, 4)})
+        del q, k, v, o
+    return out
 
 
 # --------------------------------------------------------------------------------------- CPU arms

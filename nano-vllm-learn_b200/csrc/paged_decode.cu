@@ -338,21 +338,20 @@ int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ct
       n = 148;
     sm_count = n;
   }
-  // Cost model in token units: every SM streams its CTAs' tokens back to back; a split adds a
-  // fixed overhead (prologue latency + merge + its share of the combine pass).
+  // HBM-bound kernel: what matters is enough CTAs in flight to saturate HBM (about two resident 4-warp
+  // CTAs per SM), not wave quantisation — measured on B200 (profiles/r01_decode_sweep_*.jsonl), one split
+  // is fastest as soon as (sequence, kv-head) items cover ~85 % of the SMs, because every extra split
+  // pays the partial write + combine pass.  Below that, split up to ~2 CTAs/SM, but keep >= 256 tokens
+  // of the (launch-time upper bound of the) context per split.
   const int64_t items = static_cast<int64_t>(bs) * num_kv_heads;
-  const int64_t kOverheadTokens = 96;
-  const int max_splits = max_ctx / 64 > 1 ? (max_ctx / 64 < 64 ? max_ctx / 64 : 64) : 1;
-  int best = 1;
-  int64_t best_cost = INT64_MAX;
-  for (int s = 1; s <= max_splits; ++s) {
-    const int64_t per_sm = (items * s + sm_count - 1) / sm_count;
-    const int64_t cost = per_sm * ((max_ctx + s - 1) / s + kOverheadTokens) + (s > 1 ? kOverheadTokens : 0);
-    if (cost < best_cost) {
-      best_cost = cost;
-      best = s;
-    }
-  }
+  if (items * 100 >= static_cast<int64_t>(sm_count) * 85) return 1;
+  // floor, not ceil: one full wave of (at most) two CTAs per SM; a few CTAs spilling into a second wave
+  // cannot saturate HBM on their own and double the time (bs=4 ctx=32768: 10 splits 137 us, 8 splits 105 us)
+  int64_t s = (2 * static_cast<int64_t>(sm_count)) / items;
+  const int64_t by_len = max_ctx / 256 > 1 ? max_ctx / 256 : 1;
+  if (s > by_len) s = by_len;
+  if (s > 128) s = 128;
+  const int best = static_cast<int>(s < 1 ? 1 : s);
   return best;
 }
 
