@@ -302,8 +302,21 @@ using Cfg5 = DecodeCfg<16, 2, 6>;  //  96 KB: two CTAs per SM
 using Cfg6 = DecodeCfg<16, 4, 6>;  // 192 KB
 using Cfg7 = DecodeCfg<32, 4, 2>;  // 128 KB
 constexpr int kNumVariants = 8;
-constexpr int kDefaultVariant = 0;
-static int g_variant = kDefaultVariant;
+// -1 = automatic: <16,8,3> (one 8-warp CTA per SM) when the grid fits one CTA per SM, else <16,4,3>
+// (two 4-warp CTAs per SM).  Same warps and bytes in flight per SM; measured in profiles/r01_decode_sweep_*.
+static int g_variant = -1;
+
+static int sm_count_cached() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    n = v;
+  }
+  return n;
+}
 
 template <class Cfg>
 static cudaError_t launch_decode(const DecodeParams& p, int bs, int hkv, cudaStream_t stream) {
@@ -331,23 +344,18 @@ size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads, int32
 
 int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ctx, int32_t sm_count) {
   if (bs <= 0 || num_kv_heads <= 0 || max_ctx <= 0) return 1;
-  if (sm_count <= 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
-    sm_count = n;
-  }
+  if (sm_count <= 0) sm_count = nvllm::sm_count_cached();
   // HBM-bound kernel: what matters is enough CTAs in flight to saturate HBM (about two resident 4-warp
   // CTAs per SM), not wave quantisation — measured on B200 (profiles/r01_decode_sweep_*.jsonl), one split
   // is fastest as soon as (sequence, kv-head) items cover ~85 % of the SMs, because every extra split
-  // pays the partial write + combine pass.  Below that, split up to ~2 CTAs/SM, but keep >= 256 tokens
+  // pays the partial write + combine pass.  Below that, split up to one CTA per SM, but keep >= 256 tokens
   // of the (launch-time upper bound of the) context per split.
   const int64_t items = static_cast<int64_t>(bs) * num_kv_heads;
   if (items * 100 >= static_cast<int64_t>(sm_count) * 85) return 1;
-  // floor, not ceil: one full wave of (at most) two CTAs per SM; a few CTAs spilling into a second wave
-  // cannot saturate HBM on their own and double the time (bs=4 ctx=32768: 10 splits 137 us, 8 splits 105 us)
-  int64_t s = (2 * static_cast<int64_t>(sm_count)) / items;
+  // One wave of one 8-warp CTA per SM (floor, not ceil): a few CTAs spilling into a second wave cannot
+  // saturate HBM on their own and double the time (bs=4 ctx=32768: 10 splits 137 us, 8 splits 105 us), and
+  // fewer, fatter splits mean fewer partials for the combine pass.
+  int64_t s = static_cast<int64_t>(sm_count) / items;
   const int64_t by_len = max_ctx / 256 > 1 ? max_ctx / 256 : 1;
   if (s > by_len) s = by_len;
   if (s > 128) s = 128;
@@ -356,8 +364,7 @@ int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ct
 }
 
 int nvllm_paged_decode_set_variant(int32_t variant) {
-  if (variant == -1) variant = nvllm::kDefaultVariant;
-  if (variant < 0 || variant >= nvllm::kNumVariants) return NVLLM_ERR_BAD_ARG;
+  if (variant < -1 || variant >= nvllm::kNumVariants) return NVLLM_ERR_BAD_ARG;
   nvllm::g_variant = variant;
   return NVLLM_OK;
 }
@@ -405,7 +412,10 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;
-  switch (g_variant) {
+  int variant = g_variant;
+  if (variant < 0)
+    variant = (static_cast<int64_t>(bs) * num_kv_heads * num_splits <= sm_count_cached()) ? 2 : 0;
+  switch (variant) {
     case 0: e = launch_decode<Cfg0>(p, bs, num_kv_heads, st); break;
     case 1: e = launch_decode<Cfg1>(p, bs, num_kv_heads, st); break;
     case 2: e = launch_decode<Cfg2>(p, bs, num_kv_heads, st); break;
