@@ -20,7 +20,7 @@ def _run(backend, model_dir, prompts, steps, port):
     from nanovllm import LLM, SamplingParams
     os.environ["NVLLM_PORT"] = str(port)
     llm = LLM(model_dir, enforce_eager=False, max_model_len=1024, max_num_seqs=8, attn_backend=backend,
-              gpu_memory_utilization=0.25, max_num_batched_tokens=4096)
+              max_num_batched_tokens=4096)
     rec = {}
     try:
         runner = llm.model_runner
@@ -40,6 +40,7 @@ def _run(backend, model_dir, prompts, steps, port):
         rec["tokens"] = [o["token_ids"] for o in out]
     finally:
         llm.exit()
+        runner = None          # drop the last reference to the ~160 GB kv cache before emptying the allocator
         del llm
         gc.collect()
         torch.cuda.empty_cache()
@@ -69,6 +70,8 @@ def test_engine_flash_vs_cuda(tmp_path):
     steps = 20   # decode steps: bs=3 -> graph batch 4 (one zero-padded row), crosses no block boundary for seq 0/2
 
     a = _run("flash", model_dir, prompts, steps, 2391)
+    gc.collect()
+    torch.cuda.empty_cache()
     b = _run("cuda", model_dir, prompts, steps, 2392)
     assert a["tokens"] == b["tokens"]                      # the pinned sampler ran the same number of steps
     assert a["calls"] == b["calls"] == steps
