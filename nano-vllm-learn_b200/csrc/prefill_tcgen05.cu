@@ -3,7 +3,9 @@
 // including the paged-prefix (prefix cache) form: K/V tiles come either from this step's dense k/v or
 // from the paged cache through block_tables, both via 2-D tensor maps with 128-byte swizzle.
 //
-// One CTA = one (sequence, q head, PAIR of 128-query tiles A and B).  384 threads:
+// Persistent kernel: one CTA per SM loops over work items (sequence, q head, PAIR of 128-query tiles A and
+// B); barrier phases run on across items, so the TMA producer prefetches the next item's Q/K/V while the
+// softmax warpgroups drain the current item's output.  384 threads:
 //   warpgroup 0 (warps 0-3)   softmax of tile A: one query row per thread (TMEM lane == row)
 //   warpgroup 1 (warps 4-7)   softmax of tile B
 //   warp 8                    TMA producer (one elected lane)
@@ -48,13 +50,49 @@ enum Bar : int {
   kSFull = 2 + 3 * kStages,      // [2]
   kPFull = kSFull + 2,           // [2]
   kOFull = kPFull + 2,           // [2]
-  kNumBars = kOFull + 2,
+  kQEmpty = kOFull + 2,          // [2]  Q_t no longer read by any pending MMA (persistent loop)
+  kOEmpty = kQEmpty + 2,         // [2]  epilogue of tile t has drained O_t from TMEM
+  kNumBars = kOEmpty + 2,
 };
+
+// Work item = (sequence, q head, pair of query tiles).  Items are enumerated heavy-first (late pairs see
+// the most keys under the causal mask) and adjacent ids share the sequence and kv head, so CTAs running
+// side by side hit the same K/V tiles in L2.  Every role of a CTA decodes the same item the same way.
+struct Item {
+  int seq, h, kvh, q0, k0, Lq, Lk, m0, shift, n_t[2], n_tiles;
+  bool live;
+};
+
+__device__ __forceinline__ Item decode_item(const PrefillParams& p, int w, int num_pairs, int batch) {
+  Item it;
+  const int per_pair = p.num_q_heads * batch;
+  const int mbp = num_pairs - 1 - w / per_pair;
+  const int rem = w % per_pair;
+  it.seq = rem / p.num_q_heads;
+  it.h = rem % p.num_q_heads;
+  it.kvh = it.h / p.group;
+  it.q0 = __ldg(p.cu_q + it.seq);
+  it.Lq = __ldg(p.cu_q + it.seq + 1) - it.q0;
+  it.k0 = __ldg(p.cu_k + it.seq);
+  it.Lk = __ldg(p.cu_k + it.seq + 1) - it.k0;
+  it.m0 = mbp * 2 * TM;
+  it.shift = it.Lk - it.Lq;
+  it.live = it.m0 < it.Lq;
+  const int hiA = min(it.Lk, it.shift + it.m0 + TM);
+  it.n_t[0] = (it.live && hiA > 0) ? (hiA + TN - 1) / TN : 0;
+  const int hiB = (it.m0 + TM < it.Lq) ? min(it.Lk, it.shift + it.m0 + 2 * TM) : 0;
+  it.n_t[1] = (it.live && hiB > 0) ? (hiB + TN - 1) / TN : 0;
+  it.n_tiles = max(it.n_t[0], it.n_t[1]);
+  it.live = it.live && it.n_tiles > 0;
+  return it;
+}
+
 
 template <bool kDebug>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                       const __grid_constant__ CUtensorMap tm_v, const PrefillParams p, float* __restrict__ debug) {
+                       const __grid_constant__ CUtensorMap tm_v, const PrefillParams p, const int num_pairs,
+                       const int batch, float* __restrict__ debug) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SW128 tiles need 1024-byte alignment
   unsigned char* smem_gen = smem_raw + (smem - smem_u32(smem_raw));
@@ -62,27 +100,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
-  const int mbp = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);  // heavy (late) pairs first
-  const int h = blockIdx.y;
-  const int seq = blockIdx.z;
-
-  const int q0 = __ldg(p.cu_q + seq);
-  const int Lq = __ldg(p.cu_q + seq + 1) - q0;
-  const int k0 = __ldg(p.cu_k + seq);
-  const int Lk = __ldg(p.cu_k + seq + 1) - k0;
-  const int m0 = mbp * 2 * TM;
-  if (m0 >= Lq) return;  // uniform for the CTA, before any barrier or TMEM allocation
-  const int shift = Lk - Lq;
-  const int kvh = h / p.group;
-  // keys needed by tile t: 0 .. min(Lk, shift + m0 + (t+1)*128) - 1
-  int n_t[2];
-  {
-    int hiA = min(Lk, shift + m0 + TM);
-    n_t[0] = hiA > 0 ? (hiA + TN - 1) / TN : 0;
-    int hiB = (m0 + TM < Lq) ? min(Lk, shift + m0 + 2 * TM) : 0;
-    n_t[1] = hiB > 0 ? (hiB + TN - 1) / TN : 0;
-  }
-  const int n_tiles = max(n_t[0], n_t[1]);
+  const int total_items = num_pairs * p.num_q_heads * batch;
 
   const uint32_t bar0 = smem + kSmemBar;
   auto bar = [&](int i) -> uint32_t { return bar0 + 8u * static_cast<uint32_t>(i); };
@@ -94,6 +112,8 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       tc::mbar_init(bar(kSFull + t), 1);
       tc::mbar_init(bar(kPFull + t), 128);
       tc::mbar_init(bar(kOFull + t), 1);
+      tc::mbar_init(bar(kQEmpty + t), 1);
+      tc::mbar_init(bar(kOEmpty + t), 128);
     }
     for (int s = 0; s < kStages; ++s) {
       tc::mbar_init(bar(kKFull + s), 1);
@@ -112,90 +132,110 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const uint32_t tmem = *tmem_slot;
 
   if (warp >= 8) {
-    tc::reg_dealloc<56>();
-    if (warp == 8 && lane == 0 && n_tiles > 0) {
+    tc::reg_dealloc<96>();
+    if (warp == 8 && lane == 0) {
       // ================================ TMA producer ================================
       tc::tma_prefetch_desc(&tm_q);
       tc::tma_prefetch_desc(&tm_k);
       tc::tma_prefetch_desc(&tm_v);
-      for (int t = 0; t < 2; ++t) {
-        if (n_t[t] == 0) continue;
-        const uint32_t sq = smem + kSmemQ + t * kTileBytes;
-        tc::mbar_arrive_expect_tx(bar(kQFull + t), kTileBytes);
-        tc::tma_load_2d(sq, &tm_q, h * kHeadDim, q0 + m0 + t * TM, bar(kQFull + t));
-        tc::tma_load_2d(sq + kHalfBytes, &tm_q, h * kHeadDim + 64, q0 + m0 + t * TM, bar(kQFull + t));
-      }
-      const int32_t* table = p.block_tables ? p.block_tables + static_cast<int64_t>(seq) * p.table_stride : nullptr;
-      for (int j = 0; j < n_tiles; ++j) {
-        const int st = j % kStages;
-        const uint32_t use = static_cast<uint32_t>(j / kStages);
-        tc::mbar_wait(bar(kKVEmpty + st), (use & 1u) ^ 1u);
-        int row;
-        if (table) {
-          const int t0 = j * TN;
-          row = __ldg(table + t0 / p.block_size) * p.block_size + t0 % p.block_size;
-        } else {
-          row = k0 + j * TN;
+      uint32_t kv_iter = 0;        // K/V tiles loaded so far (ring position + phase)
+      uint32_t q_uses[2] = {0, 0};  // how often Q_t has been filled
+      for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
+        const Item it = decode_item(p, w, num_pairs, batch);
+        if (!it.live) continue;
+        for (int t = 0; t < 2; ++t) {
+          if (it.n_t[t] == 0) continue;
+          tc::mbar_wait(bar(kQEmpty + t), (q_uses[t] & 1u) ^ 1u);
+          ++q_uses[t];
+          const uint32_t sq = smem + kSmemQ + t * kTileBytes;
+          tc::mbar_arrive_expect_tx(bar(kQFull + t), kTileBytes);
+          tc::tma_load_2d(sq, &tm_q, it.h * kHeadDim, it.q0 + it.m0 + t * TM, bar(kQFull + t));
+          tc::tma_load_2d(sq + kHalfBytes, &tm_q, it.h * kHeadDim + 64, it.q0 + it.m0 + t * TM, bar(kQFull + t));
         }
-        const uint32_t sk = smem + kSmemK + st * kTileBytes;
-        const uint32_t sv = smem + kSmemV + st * kTileBytes;
-        tc::mbar_arrive_expect_tx(bar(kKFull + st), kTileBytes);
-        tc::tma_load_2d(sk, &tm_k, kvh * kHeadDim, row, bar(kKFull + st));
-        tc::tma_load_2d(sk + kHalfBytes, &tm_k, kvh * kHeadDim + 64, row, bar(kKFull + st));
-        tc::mbar_arrive_expect_tx(bar(kVFull + st), kTileBytes);
-        tc::tma_load_2d(sv, &tm_v, kvh * kHeadDim, row, bar(kVFull + st));
-        tc::tma_load_2d(sv + kHalfBytes, &tm_v, kvh * kHeadDim + 64, row, bar(kVFull + st));
+        const int32_t* table =
+            p.block_tables ? p.block_tables + static_cast<int64_t>(it.seq) * p.table_stride : nullptr;
+        for (int j = 0; j < it.n_tiles; ++j, ++kv_iter) {
+          const uint32_t st = kv_iter % kStages;
+          tc::mbar_wait(bar(kKVEmpty + st), ((kv_iter / kStages) & 1u) ^ 1u);
+          int row;
+          if (table) {
+            const int t0 = j * TN;
+            row = __ldg(table + t0 / p.block_size) * p.block_size + t0 % p.block_size;
+          } else {
+            row = it.k0 + j * TN;
+          }
+          const uint32_t sk = smem + kSmemK + st * kTileBytes;
+          const uint32_t sv = smem + kSmemV + st * kTileBytes;
+          tc::mbar_arrive_expect_tx(bar(kKFull + st), kTileBytes);
+          tc::tma_load_2d(sk, &tm_k, it.kvh * kHeadDim, row, bar(kKFull + st));
+          tc::tma_load_2d(sk + kHalfBytes, &tm_k, it.kvh * kHeadDim + 64, row, bar(kKFull + st));
+          tc::mbar_arrive_expect_tx(bar(kVFull + st), kTileBytes);
+          tc::tma_load_2d(sv, &tm_v, it.kvh * kHeadDim, row, bar(kVFull + st));
+          tc::tma_load_2d(sv + kHalfBytes, &tm_v, it.kvh * kHeadDim + 64, row, bar(kVFull + st));
+        }
       }
-    } else if (warp == 9 && lane == 0 && n_tiles > 0) {
+    } else if (warp == 9 && lane == 0) {
       // ================================ MMA issuer ==================================
-      auto issue_qk = [&](int t, int j) {
-        const int st = j % kStages;
-        tc::mbar_wait(bar(kKFull + st), static_cast<uint32_t>(j / kStages) & 1u);
-        tc::fence_after_sync();
-        const uint32_t sq = smem + kSmemQ + t * kTileBytes;
-        const uint32_t sk = smem + kSmemK + st * kTileBytes;
-        const uint32_t d = tmem + static_cast<uint32_t>(t * TN);
+      uint32_t kv_base = 0;          // K/V tiles consumed by earlier items
+      uint32_t q_uses[2] = {0, 0};   // items that used tile t (phase of q_full / o_empty)
+      uint32_t p_cnt[2] = {0, 0};    // P tiles consumed per query tile (phase of p_full)
+      for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
+        const Item it = decode_item(p, w, num_pairs, batch);
+        if (!it.live) continue;
+        auto issue_qk = [&](int t, int j) {
+          const uint32_t kv = kv_base + static_cast<uint32_t>(j);
+          const uint32_t st = kv % kStages;
+          if (j == 0) tc::mbar_wait(bar(kQFull + t), q_uses[t] & 1u);
+          tc::mbar_wait(bar(kKFull + st), (kv / kStages) & 1u);
+          tc::fence_after_sync();
+          const uint32_t sq = smem + kSmemQ + t * kTileBytes;
+          const uint32_t sk = smem + kSmemK + st * kTileBytes;
+          const uint32_t d = tmem + static_cast<uint32_t>(t * TN);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint32_t off = (ks >> 2) * kHalfBytes + (ks & 3) * 32;  // 16 bf16 = 32 B inside the swizzle row
-          tc::mma_ss(d, tc::make_smem_desc(sq + off, 16, 1024), tc::make_smem_desc(sk + off, 16, 1024), kIdescQK,
-                     ks > 0 ? 1u : 0u);
-        }
-        tc::mma_commit(bar(kSFull + t));
-      };
-      auto issue_pv = [&](int t, int j) {
-        const int st = j % kStages;
-        tc::mbar_wait(bar(kVFull + st), static_cast<uint32_t>(j / kStages) & 1u);
-        tc::mbar_wait(bar(kPFull + t), static_cast<uint32_t>(j) & 1u);
-        tc::fence_after_sync();
-        const uint32_t sv = smem + kSmemV + st * kTileBytes;
-        const uint32_t d = tmem + 2u * TN + static_cast<uint32_t>(t * kHeadDim);
-        const uint32_t a = tmem + static_cast<uint32_t>(t * TN);
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint32_t off = (ks >> 2) * kHalfBytes + (ks & 3) * 32;  // 16 bf16 = 32 B inside the swizzle row
+            tc::mma_ss(d, tc::make_smem_desc(sq + off, 16, 1024), tc::make_smem_desc(sk + off, 16, 1024), kIdescQK,
+                       ks > 0 ? 1u : 0u);
+          }
+          tc::mma_commit(bar(kSFull + t));
+          if (j == it.n_t[t] - 1) tc::mma_commit(bar(kQEmpty + t));  // last read of Q_t for this item
+        };
+        auto issue_pv = [&](int t, int j) {
+          const uint32_t kv = kv_base + static_cast<uint32_t>(j);
+          const uint32_t st = kv % kStages;
+          tc::mbar_wait(bar(kVFull + st), (kv / kStages) & 1u);
+          tc::mbar_wait(bar(kPFull + t), p_cnt[t] & 1u);
+          ++p_cnt[t];
+          if (j == 0) tc::mbar_wait(bar(kOEmpty + t), (q_uses[t] & 1u) ^ 1u);  // previous item's epilogue drained O_t
+          tc::fence_after_sync();
+          const uint32_t sv = smem + kSmemV + st * kTileBytes;
+          const uint32_t d = tmem + 2u * TN + static_cast<uint32_t>(t * kHeadDim);
+          const uint32_t a = tmem + static_cast<uint32_t>(t * TN);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          // 16 keys = 16 rows of 128 B per k-step; the two 64-dim halves are kHalfBytes apart (LBO)
-          tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), tc::make_smem_desc(sv + ks * 2048, kHalfBytes, 1024),
-                     kIdescPV, (j > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < 8; ++ks) {
+            // 16 keys = 16 rows of 128 B per k-step; the two 64-dim halves are kHalfBytes apart (LBO)
+            tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), tc::make_smem_desc(sv + ks * 2048, kHalfBytes, 1024),
+                       kIdescPV, (j > 0 || ks > 0) ? 1u : 0u);
+          }
+          tc::mma_commit(bar(kOFull + t));
+        };
+        for (int t = 0; t < 2; ++t)
+          if (it.n_t[t] > 0) issue_qk(t, 0);
+        for (int j = 0; j < it.n_tiles; ++j) {
+          if (j < it.n_t[0]) issue_pv(0, j);
+          if (j + 1 < it.n_t[0]) issue_qk(0, j + 1);
+          if (j < it.n_t[1]) issue_pv(1, j);
+          tc::mma_commit(bar(kKVEmpty + (kv_base + j) % kStages));  // K_j, V_j no longer read by any pending MMA
+          if (j + 1 < it.n_t[1]) issue_qk(1, j + 1);
         }
-        tc::mma_commit(bar(kOFull + t));
-      };
-      for (int t = 0; t < 2; ++t) {
-        if (n_t[t] == 0) continue;
-        tc::mbar_wait(bar(kQFull + t), 0);
-        issue_qk(t, 0);
-      }
-      for (int j = 0; j < n_tiles; ++j) {
-        if (j < n_t[0]) issue_pv(0, j);
-        if (j + 1 < n_t[0]) issue_qk(0, j + 1);
-        if (j < n_t[1]) issue_pv(1, j);
-        tc::mma_commit(bar(kKVEmpty + j % kStages));   // K_j and V_j are no longer read by any pending MMA
-        if (j + 1 < n_t[1]) issue_qk(1, j + 1);
+        kv_base += static_cast<uint32_t>(it.n_tiles);
+        for (int t = 0; t < 2; ++t)
+          if (it.n_t[t] > 0) ++q_uses[t];
       }
     }
     __syncwarp();
   } else {
     tc::reg_alloc<200>();
-    // softmax warpgroups: body appended below
 #include "prefill_tcgen05_softmax.inl"
   }
 
@@ -259,11 +299,22 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
     if (e != cudaSuccess) return record_cuda_error(e);
     configured = true;
   }
-  dim3 grid((max_seqlen_q + 2 * TM - 1) / (2 * TM), p.num_q_heads, batch);
+  const int num_pairs = (max_seqlen_q + 2 * TM - 1) / (2 * TM);
+  const int64_t total = static_cast<int64_t>(num_pairs) * p.num_q_heads * batch;
+  if (total > INT32_MAX) return NVLLM_ERR_UNSUPPORTED;
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    sms = v;
+  }
+  const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);   // persistent: one CTA per SM
   if (g_debug)
-    prefill_tcgen05_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, g_debug);
+    prefill_tcgen05_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, g_debug);
   else
-    prefill_tcgen05_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, nullptr);
+    prefill_tcgen05_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, nullptr);
   note_launch();
   *handled = true;
   return record_cuda_error(cudaGetLastError());
