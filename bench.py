@@ -378,6 +378,7 @@ def run_tp_point(args, dev, world, rank, ops, dist):
         one(0)
     times = []
     for i in range(12):   # rotate over 4 distinct caches (>= 1.07 GB in total even at tp=8): nothing is re-read from L2
+        torch.cuda._sleep(300_000)   # GPU busy while the host queues the launch: host launch latency is not timed
         a = torch.cuda.Event(enable_timing=True)
         b = torch.cuda.Event(enable_timing=True)
         a.record()

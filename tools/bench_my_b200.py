@@ -38,9 +38,13 @@ def setup_paths(args):
             make_synthetic_model.make(args.shape, args.model_path, args.layers)
 
 
-def run_single(llm, SamplingParams, torch, input_len, num_seqs, output_len):
-    prompts = [[randint(0, 10000) for _ in range(input_len)] for _ in range(num_seqs)]
-    sps = [SamplingParams(temperature=0.0, ignore_eos=True, max_tokens=output_len) for _ in range(num_seqs)]
+def run_single(llm, SamplingParams, torch, input_len, num_seqs, output_len, shared_prefix=0, temperature=0.0):
+    # shared_prefix > 0: BASELINE configs[2] — every prompt starts with the same tokens, so all but the first
+    # sequence hit the prefix cache (cu_seqlens_k > cu_seqlens_q, block_tables set in prefill).  Keep it shorter
+    # than the prompt: a fully cached prompt trips the reference's Lq == 0 quirk.
+    shared = [randint(0, 10000) for _ in range(shared_prefix)]
+    prompts = [shared + [randint(0, 10000) for _ in range(input_len - shared_prefix)] for _ in range(num_seqs)]
+    sps = [SamplingParams(temperature=temperature, ignore_eos=True, max_tokens=output_len) for _ in range(num_seqs)]
     torch.cuda.synchronize()
     t0 = time.time()
     llm.generate(prompts, sps, use_tqdm=False)
@@ -63,7 +67,7 @@ def bench_backend(args, backend, port):
             for n in args.input_lens:
                 out_len = args.output_len or n
                 try:
-                    ms = run_single(llm, SamplingParams, torch, n, bs, out_len)
+                    ms = run_single(llm, SamplingParams, torch, n, bs, out_len, args.shared_prefix, args.temperature)
                     res[f"{bs}x{n}"] = dict(bs=bs, input_len=n, output_len=out_len, ms=round(ms, 1),
                                             tok_s=round(bs * out_len / (ms / 1000), 1))
                 except torch.cuda.OutOfMemoryError:
@@ -93,6 +97,8 @@ def main():
     ap.add_argument("--max-model-len", type=int, default=4096)
     ap.add_argument("--tensor-parallel-size", type=int, default=1)
     ap.add_argument("--enforce-eager", action="store_true")
+    ap.add_argument("--shared-prefix", type=int, default=0, help="tokens shared by all prompts (prefix-cache hits)")
+    ap.add_argument("--temperature", type=float, default=0.0)
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     setup_paths(args)
@@ -110,7 +116,8 @@ def main():
             print(row)
     if args.out:
         with open(args.out, "w") as f:
-            json.dump(dict(tp=args.tensor_parallel_size, shape=args.shape, max_model_len=args.max_model_len,
+            json.dump(dict(tp=args.tensor_parallel_size, shape=args.shape, layers=args.layers,
+                           shared_prefix=args.shared_prefix, max_model_len=args.max_model_len,
                            results=results), f, indent=1)
 
 
