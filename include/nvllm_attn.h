@@ -192,6 +192,34 @@ NVLLM_API int nvllm_varlen_prefill_set_variant(int32_t variant);
 NVLLM_API void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr);
 
 /* ------------------------------------------------------------------------
+ * (3b) fused pre-attention step (SURVEY §8f "next", rank 1): per-head q/k
+ *     RMSNorm + NeoX RoPE + store_kvcache in one launch, reading the fused
+ *     qkv projection output [n_tokens, (Hq + 2 Hkv) * head_dim] once.
+ *     reference: nanovllm/layers/layernorm.py:17-27 (RMSNorm.rms_forward per
+ *     head), nanovllm/layers/rotary_embedding.py:6-55, nanovllm/layers/
+ *     attention.py:19-55, as sequenced by nanovllm/models/qwen3.py:106-117.
+ *
+ *   q_out [n, Hq*D] receives the normalised, rotated queries; k_out (may be
+ *   NULL) the same for keys (needed by prefill without a prefix hit);
+ *   k_cache/v_cache (both NULL = no cache bound, the warmup case) receive K
+ *   (normalised, rotated) and V rows at slot_mapping[i] (negative = skip).
+ *   cos_sin_cache is the reference's fp32 [max_position, D] table
+ *   (cos | sin halves); positions are int64 as the reference feeds them.
+ *   Supported: head_dim == 128.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride,
+                             const void* q_weight, const void* k_weight,
+                             float eps, const float* cos_sin_cache,
+                             const int64_t* positions,
+                             void* q_out, int64_t q_out_stride,
+                             void* k_out, int64_t k_out_stride,
+                             void* k_cache, void* v_cache,
+                             const int32_t* slot_mapping,
+                             int32_t n_tokens, int32_t num_q_heads,
+                             int32_t num_kv_heads, int32_t head_dim,
+                             void* stream);
+
+/* ------------------------------------------------------------------------
  * (4) runner glue index math on the HOST (plain C, no CUDA): the integer
  *     arithmetic of prepare_decode / prepare_prefill, so the Python glue can
  *     fill persistent pinned staging buffers without per-step list building.

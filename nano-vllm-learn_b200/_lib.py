@@ -32,6 +32,9 @@ SIGNATURES = {
                                      c_int64, c_int32, c_int32, c_int32, c_int32, c_float, c_void_p]),
     "nvllm_varlen_prefill_set_variant": (c_int, [c_int32]),
     "nvllm_varlen_prefill_set_debug_buffer": (None, [c_void_p]),
+    "nvllm_qk_norm_rope_store": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+                                         c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
+                                         c_int32, c_int32, c_void_p]),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),
 }

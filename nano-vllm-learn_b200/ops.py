@@ -67,6 +67,44 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
     _lib.check(st, "store_kvcache")
 
 
+def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: torch.Tensor, k_weight: torch.Tensor,
+                       eps: float, cos_sin_cache: torch.Tensor, num_q_heads: int, num_kv_heads: int, head_dim: int,
+                       k_cache: Optional[torch.Tensor] = None, v_cache: Optional[torch.Tensor] = None,
+                       slot_mapping: Optional[torch.Tensor] = None, want_k: bool = True):
+    """Fused q/k RMSNorm + RoPE + store_kvcache on the fused projection output qkv [N, (Hq+2Hkv)*D].
+
+    Returns (q [N, Hq*D], k [N, Hkv*D] or None).  Reference sequence: qwen3.py:106-117 (q_norm, k_norm,
+    rotary_emb) followed by attention.py:86 (store_kvcache)."""
+    lib = _lib.load()
+    _require_cuda(qkv, positions, q_weight, k_weight, cos_sin_cache, k_cache, v_cache, slot_mapping)
+    n = qkv.shape[0]
+    assert qkv.dim() == 2 and qkv.stride(-1) == 1 and qkv.shape[1] == (num_q_heads + 2 * num_kv_heads) * head_dim
+    assert qkv.dtype == torch.bfloat16 and q_weight.dtype == torch.bfloat16 and k_weight.dtype == torch.bfloat16
+    assert q_weight.numel() == head_dim and k_weight.numel() == head_dim
+    assert q_weight.is_contiguous() and k_weight.is_contiguous()
+    assert positions.dtype == torch.int64 and positions.is_contiguous() and positions.numel() == n
+    cs = cos_sin_cache.view(cos_sin_cache.shape[0], -1)
+    assert cs.dtype == torch.float32 and cs.is_contiguous() and cs.shape[1] == head_dim
+    q = torch.empty((n, num_q_heads * head_dim), dtype=qkv.dtype, device=qkv.device)
+    k = torch.empty((n, num_kv_heads * head_dim), dtype=qkv.dtype, device=qkv.device) if want_k else None
+    kc_ptr = vc_ptr = sm_ptr = 0
+    if k_cache is not None and k_cache.numel():
+        row = num_kv_heads * head_dim
+        assert k_cache.stride(1) == row and v_cache.stride(1) == row and k_cache.stride(0) == k_cache.size(1) * row
+        assert v_cache.stride() == k_cache.stride() and k_cache.dtype == qkv.dtype
+        assert slot_mapping is not None and slot_mapping.dtype == torch.int32 and slot_mapping.is_contiguous()
+        assert slot_mapping.numel() == n
+        kc_ptr, vc_ptr, sm_ptr = k_cache.data_ptr(), v_cache.data_ptr(), slot_mapping.data_ptr()
+    if n == 0:
+        return q, k
+    st = lib.nvllm_qk_norm_rope_store(qkv.data_ptr(), qkv.stride(0), q_weight.data_ptr(), k_weight.data_ptr(), float(eps),
+                                      cs.data_ptr(), positions.data_ptr(), q.data_ptr(), q.stride(0),
+                                      k.data_ptr() if k is not None else 0, k.stride(0) if k is not None else 0,
+                                      kc_ptr, vc_ptr, sm_ptr, n, num_q_heads, num_kv_heads, head_dim, _stream())
+    _lib.check(st, "qk_norm_rope_store")
+    return q, k
+
+
 def plan_num_splits(bs: int, num_kv_heads: int, max_ctx: int) -> int:
     key = (bs, num_kv_heads, max_ctx)
     s = _PLAN_CACHE.get(key)

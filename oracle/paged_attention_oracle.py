@@ -122,6 +122,33 @@ def varlen_prefill_ref(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seq
     return out.to(q.dtype)
 
 
+def qk_norm_rope_ref(qkv: torch.Tensor, positions: torch.Tensor, q_weight: torch.Tensor, k_weight: torch.Tensor,
+                     eps: float, cos_sin_cache: torch.Tensor, num_q_heads: int, num_kv_heads: int, head_dim: int = 128):
+    """(q, k, v) after per-head RMSNorm and NeoX RoPE, each [N, heads, D] in qkv.dtype; v is a plain slice.
+    Restates RMSNorm.rms_forward (nanovllm/layers/layernorm.py:17-27: fp32 normalise, round to bf16,
+    multiply by the weight in bf16) applied per head as in qwen3.py:108-114, then
+    apply_rotary_emb / RotaryEmbedding.forward (nanovllm/layers/rotary_embedding.py:6-55: fp32,
+    y1 = x1*cos - x2*sin, y2 = x2*cos + x1*sin on the two halves, round to the input dtype)."""
+    n = qkv.shape[0]
+    qs, ks = num_q_heads * head_dim, num_kv_heads * head_dim
+    q, k, v = qkv.split([qs, ks, ks], dim=-1)
+
+    def rms(x, w):
+        xf = x.reshape(n, -1, head_dim).to(torch.float32)
+        var = xf.pow(2).mean(dim=-1, keepdim=True)
+        xf = xf * torch.rsqrt(var + eps)
+        return xf.to(qkv.dtype) * w
+
+    def rope(x):
+        cs = cos_sin_cache.view(cos_sin_cache.shape[0], -1)[positions]
+        cos, sin = cs.chunk(2, dim=-1)
+        cos, sin = cos.unsqueeze(-2), sin.unsqueeze(-2)
+        x1, x2 = torch.chunk(x.to(torch.float32), 2, dim=-1)
+        return torch.cat((x1 * cos - x2 * sin, x2 * cos + x1 * sin), dim=-1).to(x.dtype)
+
+    return rope(rms(q, q_weight)), rope(rms(k, k_weight)), v.reshape(n, num_kv_heads, head_dim)
+
+
 def decode_algorithmic_bytes(context_lens, num_q_heads: int, num_kv_heads: int, head_dim: int = 128,
                              block_size: int = 256, elem: int = 2) -> int:
     """K+V rows read once + q in + o out + context_lens + live table entries."""

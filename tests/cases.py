@@ -137,3 +137,23 @@ def make_store_case(seed: int, n: int, hkv: int, nblk: int, block_size: int = 25
     k_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
     v_cache = torch.randn(nblk, block_size, hkv, D, generator=g).to(torch.bfloat16)
     return dict(key=key, value=value, slot_mapping=slots, k_cache=k_cache, v_cache=v_cache)
+
+
+def make_pre_attention_case(seed: int = 30, n: int = 37, hq: int = 16, hkv: int = 8, nblk: int = 3, block_size: int = 256):
+    """Inputs of the fused pre-attention step: fused qkv rows, norm weights, positions, slots."""
+    g = torch.Generator().manual_seed(seed)
+    qkv = (torch.randn(n, (hq + 2 * hkv) * D, generator=g) * 1.5).to(torch.bfloat16)
+    positions = torch.randint(0, 4000, (n,), generator=g)
+    q_weight = (1 + 0.1 * torch.randn(D, generator=g)).to(torch.bfloat16)
+    k_weight = (1 + 0.1 * torch.randn(D, generator=g)).to(torch.bfloat16)
+    slots = torch.randperm(nblk * block_size, generator=g)[:n].to(torch.int32)
+    return dict(qkv=qkv, positions=positions, q_weight=q_weight, k_weight=k_weight, eps=1e-6, slots=slots,
+                hq=hq, hkv=hkv, nblk=nblk, block_size=block_size, rope_base=1000000.0, max_position=4096)
+
+
+def rope_cache(base: float, max_position: int):
+    """cos_sin_cache exactly as RotaryEmbedding.__init__ builds it (rotary_embedding.py:30-37)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, D, 2, dtype=torch.float) / D))
+    t = torch.arange(max_position, dtype=torch.float)
+    freqs = torch.einsum("i,j -> ij", t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1)

@@ -147,9 +147,36 @@ def gen_glue():
     print("glue", [t["name"] for t in out])
 
 
+def gen_pre_attention():
+    """q/k RMSNorm + RoPE through the reference's own modules, eager (TORCHDYNAMO_DISABLE=1 so that
+    @torch.compile does not need a GPU/compiler): layernorm.py RMSNorm, rotary_embedding.py RotaryEmbedding."""
+    assert os.environ.get("TORCHDYNAMO_DISABLE") == "1", "run with TORCHDYNAMO_DISABLE=1"
+    from nanovllm.layers.layernorm import RMSNorm
+    from nanovllm.layers.rotary_embedding import RotaryEmbedding
+    c = cases.make_pre_attention_case()
+    hq, hkv, d = c["hq"], c["hkv"], cases.D
+    qn, kn = RMSNorm(d, c["eps"]).to(torch.bfloat16), RMSNorm(d, c["eps"]).to(torch.bfloat16)
+    qn.weight.data, kn.weight.data = c["q_weight"].clone(), c["k_weight"].clone()
+    rot = RotaryEmbedding(d, d, c["max_position"], c["rope_base"])
+    assert torch.equal(rot.cos_sin_cache, cases.rope_cache(c["rope_base"], c["max_position"]))
+    q, k, v = c["qkv"].split([hq * d, hkv * d, hkv * d], dim=-1)
+    with torch.no_grad():
+        qr = qn(q.view(-1, hq, d)).view(q.shape)
+        kr = kn(k.view(-1, hkv, d)).view(k.shape)
+        qr, kr = rot(c["positions"], qr, kr)
+    np.savez_compressed(os.path.join(HERE, "pre_attention.npz"), q=cases.bf16_bits(qr), k=cases.bf16_bits(kr),
+                        inputs_sha=cases.sha(c["qkv"], c["positions"], c["q_weight"], c["k_weight"]),
+                        meta=json.dumps(META))
+    print("pre_attention", tuple(qr.shape), tuple(kr.shape))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--pre-attention-only" in sys.argv:
+        gen_pre_attention()
+        sys.exit(0)
     gen_decode()
     gen_prefill()
     gen_gather()
     gen_glue()
+    gen_pre_attention()

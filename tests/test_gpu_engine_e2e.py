@@ -47,7 +47,11 @@ def _run(backend, model_dir, prompts, steps, port):
     return rec
 
 
-def test_engine_flash_vs_cuda(tmp_path):
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_engine_flash_vs_cuda(tmp_path, fused):
+    """fused="0": reference norm/rope kernels + cuda store/attention -> layer-0 K and V bit-exact.
+    fused="1": the §8f fused q/k-norm + RoPE + store kernel -> V bit-exact, K within 1 bf16 ulp."""
+    os.environ["NVLLM_FUSED_PRE_ATTN"] = fused
     ref = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.isdir(os.path.join(ref, "nanovllm")):
         pytest.skip("baseline/_ref not present")
@@ -76,8 +80,15 @@ def test_engine_flash_vs_cuda(tmp_path):
     assert a["tokens"] == b["tokens"]                      # the pinned sampler ran the same number of steps
     assert a["calls"] == b["calls"] == steps
     ka, kb = a["kv"], b["kv"]
-    # layer 0: bit-exact (store kernel + glue slot mapping in situ)
-    assert torch.equal(ka[:, 0].view(torch.int16), kb[:, 0].view(torch.int16))
+    # layer 0: bit-exact (store kernel + glue slot mapping in situ); V always, K when the reference's own
+    # norm/rope kernels produced it
+    assert torch.equal(ka[1, 0].view(torch.int16), kb[1, 0].view(torch.int16))
+    if fused == "0":
+        assert torch.equal(ka[0, 0].view(torch.int16), kb[0, 0].view(torch.int16))
+    else:
+        d = (ka[0, 0].float() - kb[0, 0].float()).abs()
+        assert (d <= torch.maximum(ka[0, 0].float().abs(), kb[0, 0].float().abs()) * 2.0 ** -7 + 1e-30).all()
+        assert (d > 0).float().mean().item() <= 0.02
     # deeper layers see attention outputs: bf16 tolerance
     assert (ka.float() - kb.float()).abs().max().item() <= 5e-2
     la, lb = a["logits"], b["logits"]

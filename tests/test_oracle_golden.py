@@ -111,3 +111,17 @@ def test_live_reference_if_present():
                                            causal=False, sdpa_backend=SDPBackend.MATH).squeeze(1)
     got = orc.paged_decode_ref(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], c["scale"])
     assert (got.float() - ref.float()).abs().max().item() <= TOL
+
+
+def test_pre_attention_oracle_matches_reference_fixture():
+    """q/k RMSNorm + RoPE restatement vs the reference modules' own output: bit-exact."""
+    c = cases.make_pre_attention_case()
+    g = _load("pre_attention.npz")
+    assert str(g["inputs_sha"]) == cases.sha(c["qkv"], c["positions"], c["q_weight"], c["k_weight"])
+    cs = cases.rope_cache(c["rope_base"], c["max_position"])
+    q, k, v = orc.qk_norm_rope_ref(c["qkv"], c["positions"], c["q_weight"], c["k_weight"], c["eps"], cs,
+                                   c["hq"], c["hkv"])
+    n = c["qkv"].shape[0]
+    assert torch.equal(q.reshape(n, -1).view(torch.int16), torch.from_numpy(g["q"].copy()))
+    assert torch.equal(k.reshape(n, -1).view(torch.int16), torch.from_numpy(g["k"].copy()))
+    assert torch.equal(v.reshape(n, -1), c["qkv"][:, (c["hq"] + c["hkv"]) * 128:])

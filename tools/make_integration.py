@@ -3,7 +3,7 @@
     python tools/make_integration.py [--src baseline/_ref] [--dst build/nanovllm_cuda]
 
 Copies `<src>/nanovllm` to `<dst>/nanovllm` (git-ignored, never committed) and applies exactly the
-edits a maintainer would make to admit `--attn-backend cuda` (A1-A4), plus two environment-compat
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusion A5), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
 anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
@@ -34,6 +34,13 @@ EDITS = [
      '\n\n# --- cuda attention backend: B200-native prepare/capture glue (other backends keep the methods above)\n'
      'from nano_vllm_learn_b200.runner_glue import install as _install_cuda_glue\n'
      '_install_cuda_glue(ModelRunner, set_context, get_context, reset_context)\n'),
+    # ---- A5 (optional: NVLLM_FUSED_PRE_ATTN=0 keeps the reference's separate kernels):
+    #      q/k RMSNorm + RoPE + store_kvcache fused into one launch before attention (nanovllm/models/qwen3.py:105-118)
+    ("nanovllm/models/qwen3.py",
+     '        qkv = self.qkv_proj(hidden_states)\n',
+     '        qkv = self.qkv_proj(hidden_states)\n'
+     '        if self.attn_backend == "cuda" and __import__("os").environ.get("NVLLM_FUSED_PRE_ATTN", "1") != "0":\n'
+     '            return self.o_proj(self.attn.forward_fused(qkv, positions, self.q_norm, self.k_norm, self.rotary_emb))\n'),
     # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
     ("nanovllm/config.py",
      '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',

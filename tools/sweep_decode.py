@@ -70,7 +70,7 @@ def main():
     for s in args.shapes.split(","):
         sel += shapes[s]
     nvar = lib.nvllm_paged_decode_num_variants()
-    variants = list(range(nvar)) if args.variants == "all" else [int(v) for v in args.variants.split(",")]
+    variants = list(range(nvar)) if args.variants == "all" else [int(v) for v in args.variants.split(",")]   # -1 = auto
     fa = None
     if args.flash:
         try:
