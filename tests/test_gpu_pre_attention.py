@@ -1,7 +1,7 @@
 """GPU: fused q/k RMSNorm + RoPE + store kernel vs the oracle and the fixture frozen
 from the reference's RMSNorm / RotaryEmbedding modules.  V rows are pure data movement (bit-exact); q/k
-are fp32 arithmetic rounded to bf16: at most 1 bf16 ulp from the reference on a tiny fraction of elements
-(the fp32 sum-of-squares is reduced in a different order)."""
+are fp32 arithmetic rounded to bf16 three times (norm, weight, rope): the fp32 sum-of-squares is reduced in
+a different order, so an intermediate may round the other way — at most 2 bf16 ulp on < 1 % of elements."""
 import os
 
 import numpy as np
@@ -19,8 +19,10 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 def _ulp_check(got, want, max_frac=0.01):
     got, want = got.float().cpu(), want.float().cpu()
     diff = (got - want).abs()
-    ulp = torch.maximum(got.abs(), want.abs()) * 2.0 ** -7 + 1e-30      # 1 bf16 ulp (8 bits of precision)
-    assert (diff <= ulp).all(), f"more than 1 bf16 ulp off: max diff {diff.max().item()}"
+    # RoPE combines two elements (x1*cos - x2*sin), so the error scale of an output is the magnitude of its
+    # inputs, not of the (possibly cancelled) result: 2 bf16 ulp of the head row's largest element
+    ulp = want.abs().amax(dim=-1, keepdim=True) * 2.0 ** -6 + 1e-30
+    assert (diff <= ulp).all(), f"more than 2 bf16 ulp (of the row scale) off: max diff {diff.max().item()}"
     assert (diff > 0).float().mean().item() <= max_frac
 
 

@@ -63,6 +63,12 @@ def bench_backend(args, backend, port):
               max_num_batched_tokens=max(16384, args.max_model_len))
     try:
         llm.generate(["warmup"], SamplingParams(max_tokens=1))
+        if not args.no_shape_warmup:
+            # one untimed short run per batch size (same for every backend): torch.compile re-specialises the
+            # reference's RMSNorm/RoPE/SiLU kernels on first sight of a shape, which otherwise lands in the
+            # first timed point of each backend (visible as a 2x outlier in profiles/r01_bench_my_tp1_*).
+            for bs in args.batch_sizes:
+                run_single(llm, SamplingParams, torch, args.input_lens[0], bs, 8, args.shared_prefix, args.temperature)
         for bs in args.batch_sizes:
             for n in args.input_lens:
                 out_len = args.output_len or n
@@ -99,6 +105,7 @@ def main():
     ap.add_argument("--enforce-eager", action="store_true")
     ap.add_argument("--shared-prefix", type=int, default=0, help="tokens shared by all prompts (prefix-cache hits)")
     ap.add_argument("--temperature", type=float, default=0.0)
+    ap.add_argument("--no-shape-warmup", action="store_true", help="measure exactly like bench_my.py (first point includes compiles)")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     setup_paths(args)
