@@ -197,7 +197,7 @@ def run_cuda(args):
     splits = args.splits if args.splits > 0 else ops.plan_num_splits(wl.bs, wl.hkv, wl.tables.size(1) * BLOCK)
     out = torch.empty(wl.bs, wl.hq, D, dtype=torch.bfloat16, device=dev)
     ws_bytes = ops.decode_workspace_bytes(wl.bs, wl.hq, D, splits)
-    ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream()
 
     def step(events=None):
@@ -368,7 +368,7 @@ def run_tp_point(args, dev, world, rank, ops, dist):
     scale = D ** -0.5
     splits = ops.plan_num_splits(bs, hkv, wl.tables.size(1) * BLOCK)
     out = torch.empty(bs, hq, D, dtype=torch.bfloat16, device=dev)
-    ws = torch.empty(max(ops.decode_workspace_bytes(bs, hq, D, splits), 16), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(max(ops.decode_workspace_bytes(bs, hq, D, splits), 16), dtype=torch.uint8, device=dev)
 
     def one(l):
         ops.flash_attn_with_kvcache(wl.q[l].view(bs, hq, D), wl.kv[0, l], wl.kv[1, l], wl.lens, wl.tables,

@@ -16,7 +16,8 @@
 //    S = Q.K^T and O += P.V run on the tensor cores with fp32 accumulation; online softmax between
 //    them uses warp shuffles only.
 //  * warps merge their (m, l, O) in shared memory once; with num_splits > 1 the CTA writes a
-//    normalised partial + log2-sum-exp and a small combine kernel merges the splits.
+//    normalised partial + log2-sum-exp, and the last split CTA of a (sequence, kv head) to arrive
+//    (atomic counter in the workspace, self-resetting) merges the splits — no second launch.
 #include "common.cuh"
 
 namespace nvllm {
@@ -34,6 +35,7 @@ struct DecodeParams {
   __nv_bfloat16* out;  // [bs, Hq, 128]
   float* part_o;       // [bs, Hq, S, 128]
   float* part_lse;     // [bs, Hq, S]   (log2 units)
+  int32_t* counters;   // [bs, Hkv] arrival counters of the splits; zero between launches
   int32_t num_q_heads;
   int32_t group;       // G = Hq / Hkv
   int32_t block_size;
@@ -267,29 +269,42 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
       if (d == 0) p.part_lse[slot] = den > 0.f ? M * p.scale_log2 + fast_log2(den) : -INFINITY;
     }
   }
-}
+  if (p.num_splits == 1) return;
 
-// Merge the split partials: out = sum_s 2^(lse_s - L) O_s / sum_s 2^(lse_s - L).
-// grid (bs * Hq), block 128 (one thread per head-dim element).
-__global__ void __launch_bounds__(kHeadDim) paged_decode_combine_kernel(const float* __restrict__ part_o,
-                                                                        const float* __restrict__ part_lse,
-                                                                        __nv_bfloat16* __restrict__ out,
-                                                                        int32_t num_splits) {
-  const int64_t row = blockIdx.x;
-  const int d = threadIdx.x;
-  const float* lse = part_lse + row * num_splits;
-  float L = -INFINITY;
-  for (int s = 0; s < num_splits; ++s) L = fmaxf(L, __ldg(lse + s));
-  float num = 0.f, den = 0.f;
-  if (L > -INFINITY) {
-    const float* po = part_o + row * num_splits * kHeadDim + d;
-    for (int s = 0; s < num_splits; ++s) {
-      const float w = fast_exp2(__ldg(lse + s) - L);
-      num += w * __ldg(po + static_cast<int64_t>(s) * kHeadDim);
-      den += w;
-    }
+  // ---- fused combine: the LAST split CTA of this (sequence, kv head) to arrive merges all partials.
+  // out = sum_s 2^(lse_s - L) O_s / sum_s 2^(lse_s - L).  Saves the separate combine launch (5-6 us).
+  __shared__ int s_is_last;
+  __threadfence();   // partials of this thread are visible device-wide before the arrival below
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int32_t* cnt = p.counters + b * gridDim.y + kvh;
+    const int old = atomicAdd(cnt, 1);
+    s_is_last = (old == p.num_splits - 1);
+    if (s_is_last) *cnt = 0;   // self-resetting: the next launch (or graph replay) starts from zero
   }
-  out[row * kHeadDim + d] = __float2bfloat16_rn(den > 0.f ? num / den : 0.f);
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();   // acquire side: order the partial reads after the counter observation
+  for (int idx = threadIdx.x; idx < G * kHeadDim; idx += WARPS * 32) {
+    const int row = idx >> 7;
+    const int d = idx & (kHeadDim - 1);
+    const int64_t base = (static_cast<int64_t>(b) * p.num_q_heads + kvh * G + row) * p.num_splits;
+    const float* lse = p.part_lse + base;
+    float L = -INFINITY;
+    for (int sp = 0; sp < p.num_splits; ++sp) L = fmaxf(L, __ldcg(lse + sp));
+    float num = 0.f, den = 0.f;
+    if (L > -INFINITY) {
+      const float* po = p.part_o + base * kHeadDim + d;
+#pragma unroll 4
+      for (int sp = 0; sp < p.num_splits; ++sp) {
+        const float w = fast_exp2(__ldcg(lse + sp) - L);
+        num += w * __ldcg(po + static_cast<int64_t>(sp) * kHeadDim);
+        den += w;
+      }
+    }
+    p.out[(static_cast<int64_t>(b) * p.num_q_heads + kvh * G + row) * kHeadDim + d] =
+        __float2bfloat16_rn(den > 0.f ? num / den : 0.f);
+  }
 }
 
 // ---- variants -------------------------------------------------------------------------------
@@ -339,7 +354,9 @@ extern "C" {
 size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads, int32_t head_dim, int32_t num_splits) {
   if (bs <= 0 || num_q_heads <= 0 || head_dim <= 0 || num_splits <= 1) return 0;
   const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
-  return rows * head_dim * sizeof(float) + rows * sizeof(float);
+  // partial O | partial LSE | per-(sequence, kv head) arrival counters (<= bs * Hq int32, 16-byte rounded)
+  const size_t counters = (static_cast<size_t>(bs) * num_q_heads * sizeof(int32_t) + 15) & ~static_cast<size_t>(15);
+  return rows * head_dim * sizeof(float) + ((rows * sizeof(float) + 15) & ~static_cast<size_t>(15)) + counters;
 }
 
 int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ctx, int32_t sm_count) {
@@ -403,7 +420,14 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
   p.context_lens = context_lens;
   p.out = static_cast<__nv_bfloat16*>(out);
   p.part_o = static_cast<float*>(workspace);
-  p.part_lse = num_splits > 1 ? p.part_o + static_cast<size_t>(bs) * num_q_heads * num_splits * head_dim : nullptr;
+  p.part_lse = nullptr;
+  p.counters = nullptr;
+  if (num_splits > 1) {
+    const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
+    p.part_lse = p.part_o + rows * head_dim;
+    p.counters = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(p.part_lse) +
+                                            ((rows * sizeof(float) + 15) & ~static_cast<size_t>(15)));
+  }
   p.num_q_heads = num_q_heads;
   p.group = G;
   p.block_size = block_size;
@@ -426,13 +450,6 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
     default: e = launch_decode<Cfg7>(p, bs, num_kv_heads, st); break;
   }
   note_launch();
-  if (e != cudaSuccess) return record_cuda_error(e);
-  if (num_splits > 1) {
-    paged_decode_combine_kernel<<<static_cast<unsigned>(bs * num_q_heads), kHeadDim, 0, st>>>(
-        p.part_o, p.part_lse, p.out, num_splits);
-    note_launch();
-    e = cudaGetLastError();
-  }
   return record_cuda_error(e);
 }
 

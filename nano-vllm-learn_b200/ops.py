@@ -15,6 +15,22 @@ import torch
 from . import _lib
 
 _PLAN_CACHE: dict[tuple[int, int, int], int] = {}
+# Split-KV workspace, one per device, shared by all layers (they run back to back on one stream).  It is
+# zero-filled once (the kernel's arrival counters reset themselves) and only ever grows; superseded buffers
+# stay referenced because captured CUDA graphs may still point at them.
+_WORKSPACE: dict[int, torch.Tensor] = {}
+_RETIRED_WORKSPACES: list[torch.Tensor] = []
+
+
+def _decode_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _WORKSPACE.get(idx)
+    if ws is None or ws.numel() < nbytes:
+        if ws is not None:
+            _RETIRED_WORKSPACES.append(ws)
+        ws = torch.zeros(max(nbytes, 4 << 20), dtype=torch.uint8, device=device)
+        _WORKSPACE[idx] = ws
+    return ws
 
 
 def _stream() -> int:
@@ -153,8 +169,9 @@ def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: tor
     ws_bytes = decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits)
     ws_ptr = 0
     if ws_bytes:
+        # a caller-provided workspace must have been zero-filled once (see include/nvllm_attn.h)
         if workspace is None or workspace.numel() * workspace.element_size() < ws_bytes:
-            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)
+            workspace = _decode_workspace(q.device, ws_bytes)
         ws_ptr = workspace.data_ptr()
         ws_bytes = workspace.numel() * workspace.element_size()
     st = lib.nvllm_paged_decode(out.data_ptr(), q3.data_ptr(), q3.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),

@@ -97,7 +97,7 @@ def main():
                 if ctx // ns < 32 or (s > 0 and ns in done):
                     continue
                 done.add(ns)
-                ws = torch.empty(max(ops.decode_workspace_bytes(bs, hq, D, ns), 16), dtype=torch.uint8, device=dev)
+                ws = torch.zeros(max(ops.decode_workspace_bytes(bs, hq, D, ns), 16), dtype=torch.uint8, device=dev)
                 f = lambda i: ops.flash_attn_with_kvcache(sets[i % ncopy][0], sets[i % ncopy][1], sets[i % ncopy][2], lens,
                                                           sets[i % ncopy][4], softmax_scale=D ** -0.5, num_splits=ns,
                                                           out=out, workspace=ws)
