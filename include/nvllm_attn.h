@@ -117,8 +117,8 @@ NVLLM_API int nvllm_store_kvcache(const void* key, int64_t key_row_stride,
  *   share of the LIVE ctx_b (not of the table width).  num_splits > 1 needs a
  *   workspace of nvllm_paged_decode_workspace_bytes(); the last split CTA
  *   of each (sequence, kv head) merges the partials inside the same launch.
- *   The workspace must be ZERO-FILLED ONCE before its first use (it holds
- *   self-resetting arrival counters after the partials) and must not be
+ *   The workspace must be ZERO-FILLED ONCE before its first use (its first 64 KiB
+ *   hold self-resetting arrival counters, then the partials) and must not be
  *   shared by launches that may run concurrently.
  *   Supported: head_dim == 128, G in {1,2,4,8}, block_size % 32 == 0.
  * ---------------------------------------------------------------------- */

@@ -316,6 +316,7 @@ using Cfg4 = DecodeCfg<32, 2, 3>;  //  96 KB: two CTAs per SM
 using Cfg5 = DecodeCfg<16, 2, 6>;  //  96 KB: two CTAs per SM
 using Cfg6 = DecodeCfg<16, 4, 6>;  // 192 KB
 using Cfg7 = DecodeCfg<32, 4, 2>;  // 128 KB
+constexpr size_t kCounterBytes = 65536;   // 16384 (sequence, kv head) arrival counters
 constexpr int kNumVariants = 8;
 // -1 = automatic: <16,8,3> (one 8-warp CTA per SM) when the grid fits one CTA per SM, else <16,4,3>
 // (two 4-warp CTAs per SM).  Same warps and bytes in flight per SM; measured in profiles/r01_decode_sweep_*.
@@ -354,9 +355,9 @@ extern "C" {
 size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads, int32_t head_dim, int32_t num_splits) {
   if (bs <= 0 || num_q_heads <= 0 || head_dim <= 0 || num_splits <= 1) return 0;
   const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
-  // partial O | partial LSE | per-(sequence, kv head) arrival counters (<= bs * Hq int32, 16-byte rounded)
-  const size_t counters = (static_cast<size_t>(bs) * num_q_heads * sizeof(int32_t) + 15) & ~static_cast<size_t>(15);
-  return rows * head_dim * sizeof(float) + ((rows * sizeof(float) + 15) & ~static_cast<size_t>(15)) + counters;
+  // [fixed 64 KiB of per-(sequence, kv head) arrival counters] | partial O | partial LSE.  The counter area
+  // sits at a geometry-independent place so one zero-filled workspace can serve calls of any shape.
+  return nvllm::kCounterBytes + rows * head_dim * sizeof(float) + rows * sizeof(float);
 }
 
 int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ctx, int32_t sm_count) {
@@ -423,10 +424,11 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
   p.part_lse = nullptr;
   p.counters = nullptr;
   if (num_splits > 1) {
+    if (static_cast<size_t>(bs) * num_kv_heads * sizeof(int32_t) > kCounterBytes) return NVLLM_ERR_UNSUPPORTED;
     const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
+    p.counters = static_cast<int32_t*>(workspace);
+    p.part_o = reinterpret_cast<float*>(static_cast<char*>(workspace) + kCounterBytes);
     p.part_lse = p.part_o + rows * head_dim;
-    p.counters = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(p.part_lse) +
-                                            ((rows * sizeof(float) + 15) & ~static_cast<size_t>(15)));
   }
   p.num_q_heads = num_q_heads;
   p.group = G;

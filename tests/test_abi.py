@@ -57,7 +57,7 @@ def test_argument_validation_without_gpu(lib):
     assert dec(splits=0) == 1
     assert dec(splits=4) == 5                # workspace required
     assert lib.nvllm_paged_decode_workspace_bytes(2, 16, 128, 1) == 0
-    assert lib.nvllm_paged_decode_workspace_bytes(2, 16, 128, 4) == 2 * 16 * 4 * (128 * 4 + 4) + 2 * 16 * 4
+    assert lib.nvllm_paged_decode_workspace_bytes(2, 16, 128, 4) == 65536 + 2 * 16 * 4 * (128 * 4 + 4)
     # prefill
     def pre(batch=1, mq=8, d=128, hq=4, hkv=2, bt=None, bsz=0):
         return lib.nvllm_varlen_prefill(16, 16, 512, 16, 256, 16, 256, 0, 16, 16, batch, 8, 8, mq, mq, bt, 0, hq, hkv, d,

@@ -374,8 +374,10 @@ def test_prefill_zero_length_sequence(ops):
 
 # ------------------------------------------------------------------ the Attention module (drop-in boundary)
 def test_attention_module_prefill_then_decode(ops):
-    from nano_vllm_learn_b200 import set_context, reset_context
+    from nano_vllm_learn_b200 import set_context, reset_context, get_context
+    from nano_vllm_learn_b200 import attention_cuda
     from nano_vllm_learn_b200.attention_cuda import Attention
+    attention_cuda.bind_context(get_context)   # the engine e2e test may have bound nanovllm's context in this process
     hq, hkv, nblk = 16, 8, 12
     attn = Attention(hq, 128, 128 ** -0.5, hkv)
     assert attn.k_cache.numel() == 0 and attn.v_cache.numel() == 0
