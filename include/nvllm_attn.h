@@ -250,6 +250,12 @@ NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
                                     int32_t block_size, int32_t* slots_out,
                                     int64_t capacity);
 
+/* Measurement aid (tools/membench.py), not on the product path: streams `bytes`
+ * of `buf` with contiguous warp reads (pattern 0) or with the decode kernel's
+ * 256-byte-row / token-stride access shape (pattern 1, hkv heads). */
+NVLLM_API int nvllm_debug_stream_read(const void* buf, int64_t bytes, int32_t pattern,
+                            int32_t hkv, int32_t blocks, void* sink, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
