@@ -48,8 +48,8 @@ enum Bar : int {
   kVFull = 2 + kStages,          // [kStages]
   kKVEmpty = 2 + 2 * kStages,    // [kStages]
   kSFull = 2 + 3 * kStages,      // [2]
-  kPFull = kSFull + 2,           // [2 tiles][2 halves]: P columns 0-31 (keys 0-63) / 32-63 (keys 64-127) written
-  kOFull = kPFull + 4,           // [2]
+  kPFull = kSFull + 2,           // [2]
+  kOFull = kPFull + 2,           // [2]
   kQEmpty = kOFull + 2,          // [2]  Q_t no longer read by any pending MMA (persistent loop)
   kOEmpty = kQEmpty + 2,         // [2]  epilogue of tile t has drained O_t from TMEM
   kNumBars = kOEmpty + 2,
@@ -110,8 +110,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     for (int t = 0; t < 2; ++t) {
       tc::mbar_init(bar(kQFull + t), 1);
       tc::mbar_init(bar(kSFull + t), 1);
-      tc::mbar_init(bar(kPFull + 2 * t), 128);
-      tc::mbar_init(bar(kPFull + 2 * t + 1), 128);
+      tc::mbar_init(bar(kPFull + t), 128);
       tc::mbar_init(bar(kOFull + t), 1);
       tc::mbar_init(bar(kQEmpty + t), 1);
       tc::mbar_init(bar(kOEmpty + t), 128);
@@ -205,24 +204,19 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           const uint32_t kv = kv_base + static_cast<uint32_t>(j);
           const uint32_t st = kv % kStages;
           tc::mbar_wait(bar(kVFull + st), (kv / kStages) & 1u);
+          tc::mbar_wait(bar(kPFull + t), p_cnt[t] & 1u);
+          ++p_cnt[t];
           if (j == 0) tc::mbar_wait(bar(kOEmpty + t), (q_uses[t] & 1u) ^ 1u);  // previous item's epilogue drained O_t
+          tc::fence_after_sync();
           const uint32_t sv = smem + kSmemV + st * kTileBytes;
           const uint32_t d = tmem + 2u * TN + static_cast<uint32_t>(t * kHeadDim);
           const uint32_t a = tmem + static_cast<uint32_t>(t * TN);
-          // P arrives in two halves (keys 0-63, 64-127): the first four k-steps run on the tensor pipe while
-          // the softmax warpgroup is still exponentiating the second half
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            tc::mbar_wait(bar(kPFull + 2 * t + half), p_cnt[t] & 1u);
-            tc::fence_after_sync();
-#pragma unroll
-            for (int ks = half * 4; ks < half * 4 + 4; ++ks) {
-              // 16 keys = 16 rows of 128 B per k-step; the two 64-dim halves are kHalfBytes apart (LBO)
-              tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), tc::make_smem_desc(sv + ks * 2048, kHalfBytes, 1024),
-                         kIdescPV, (j > 0 || ks > 0) ? 1u : 0u);
-            }
+          for (int ks = 0; ks < 8; ++ks) {
+            // 16 keys = 16 rows of 128 B per k-step; the two 64-dim halves are kHalfBytes apart (LBO)
+            tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), tc::make_smem_desc(sv + ks * 2048, kHalfBytes, 1024),
+                       kIdescPV, (j > 0 || ks > 0) ? 1u : 0u);
           }
-          ++p_cnt[t];
           tc::mma_commit(bar(kOFull + t));
         };
         for (int t = 0; t < 2; ++t)

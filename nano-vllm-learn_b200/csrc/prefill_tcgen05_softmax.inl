@@ -87,15 +87,10 @@
           pk[i] = pack_bf16x2(p0, p1);
         }
         tc::tmem_st16(s_addr + cc * 16, pk);
-        if (cc == 1) {  // keys 0-63 of P (and any O rescale) are in TMEM: PV may start on them
-          tc::tmem_st_wait();
-          tc::fence_before_sync();
-          tc::mbar_arrive(bar(kPFull + 2 * t));
-        }
       }
       tc::tmem_st_wait();
       tc::fence_before_sync();
-      tc::mbar_arrive(bar(kPFull + 2 * t + 1));
+      tc::mbar_arrive(bar(kPFull + t));
       l_run += psum0 + psum1;
     }
 
