@@ -102,7 +102,7 @@ class ClockSampler:
             os.close(fd)
             self.out = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=self.out,
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=self.out,
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None

@@ -30,6 +30,8 @@ class Context:
     block_tables: Optional[torch.Tensor] = None
 
 
+# One record per process: each tensor-parallel rank is its own spawned process (llm_engine.py:29-36) and runs
+# a single Python thread, so a module-level slot is all the engine needs.
 _ACTIVE = Context()
 
 
@@ -46,4 +48,6 @@ def set_context(is_prefill, cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=0
 
 def reset_context() -> None:
     global _ACTIVE
-    _ACTIVE = Context()
+    # One record per process: each tensor-parallel rank is its own spawned process (llm_engine.py:29-36) and runs
+# a single Python thread, so a module-level slot is all the engine needs.
+_ACTIVE = Context()
