@@ -331,14 +331,46 @@ def run_e2e(args, wl, dev, Attention, set_context, reset_context, scale, dist):
     d2h = h_out.numel() * 2
     kd = wl.hkv * D
 
+    # Copies overlap compute on their own streams: the step's inputs are staged host->device on `up` (one event
+    # per layer), the kernels run on the current stream, each layer's output goes device->host on `down`.
+    # Every byte still moves inside the timed region; double-buffered device staging (2 x L slots) keeps a
+    # step's uploads from overwriting inputs the previous step is still reading.
+    cur = torch.cuda.current_stream()
+    up, down = torch.cuda.Stream(), torch.cuda.Stream()
+    d_q = torch.empty((2,) + tuple(h_q.shape), dtype=h_q.dtype, device=dev)
+    d_kv = torch.empty((2,) + tuple(h_kv.shape), dtype=h_kv.dtype, device=dev)
+    d_o = torch.empty((2, wl.layers, wl.bs, wl.hq * D), dtype=torch.bfloat16, device=dev)
+    d_slots, d_lens, d_tab = (torch.empty_like(t, device=dev) for t in (h_slots, h_lens, h_tab))
+    ev_in = [[torch.cuda.Event() for _ in range(wl.layers)] for _ in range(2)]
+    ev_out = [[torch.cuda.Event() for _ in range(wl.layers)] for _ in range(2)]
+    ev_meta, ev_done = torch.cuda.Event(), [torch.cuda.Event(), torch.cuda.Event()]
+    state = {"n": 0}
+
     def step():
-        set_context(False, slot_mapping=h_slots.to(dev, non_blocking=True),
-                    context_lens=h_lens.to(dev, non_blocking=True), block_tables=h_tab.to(dev, non_blocking=True))
+        par = state["n"] & 1
+        state["n"] += 1
+        up.wait_event(ev_done[par])            # slot `par` was last read two steps ago
+        with torch.cuda.stream(up):
+            d_slots.copy_(h_slots, non_blocking=True)
+            d_lens.copy_(h_lens, non_blocking=True)
+            d_tab.copy_(h_tab, non_blocking=True)
+            ev_meta.record(up)
+            for l in range(wl.layers):
+                d_q[par, l].copy_(h_q[l], non_blocking=True)
+                d_kv[par, l].copy_(h_kv[l], non_blocking=True)
+                ev_in[par][l].record(up)
+        cur.wait_event(ev_meta)
+        set_context(False, slot_mapping=d_slots, context_lens=d_lens, block_tables=d_tab)
         for l in range(wl.layers):
-            q = h_q[l].to(dev, non_blocking=True)
-            kvr = h_kv[l].to(dev, non_blocking=True)
-            o = attn[l](q, kvr[:, :kd], kvr[:, kd:])
-            h_out[l].copy_(o, non_blocking=True)
+            cur.wait_event(ev_in[par][l])
+            kvr = d_kv[par, l]
+            d_o[par, l].copy_(attn[l](d_q[par, l], kvr[:, :kd], kvr[:, kd:]))
+            ev_out[par][l].record(cur)
+            down.wait_event(ev_out[par][l])
+            with torch.cuda.stream(down):
+                h_out[l].copy_(d_o[par, l], non_blocking=True)
+        ev_done[par].record(cur)
+        cur.wait_stream(down)                  # the step is over when its last output byte is on the host
         reset_context()
 
     with torch.inference_mode():
@@ -356,7 +388,8 @@ def run_e2e(args, wl, dev, Attention, set_context, reset_context, scale, dist):
         torch.cuda.synchronize()
     return {"_ms": t0.elapsed_time(t1) / args.steps, "unit": UNIT, "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h,
-            "api": "nano_vllm_learn_b200.attention_cuda.Attention.forward + Context, pinned host q/k/v in, output out"}
+            "api": "nano_vllm_learn_b200.attention_cuda.Attention.forward + Context, pinned host q/k/v in, output out; "
+                   "H2D / compute / D2H on three streams"}
 
 
 def run_tp_point(args, dev, world, rank, ops, dist):
