@@ -42,20 +42,6 @@ constexpr float kRescaleThreshold = 8.f;     // log2 units: P stays <= 2^8 relat
 constexpr uint32_t kIdescQK = tc::make_idesc_bf16(TM, TN, /*b_mn_major=*/false);
 constexpr uint32_t kIdescPV = tc::make_idesc_bf16(TM, kHeadDim, /*b_mn_major=*/true);
 
-// exp2 on the FMA/ALU pipes for a fraction of the scores (the MUFU/XU pipe is shared by both softmax
-// warpgroups): round-to-nearest split x = n + f, f in [-0.5, 0.5], degree-3 polynomial for 2^f (relative error
-// 1e-4, far below the bf16 rounding of P), exponent bits of n added to the result.
-constexpr int kPolyMask = 1;   // odd-indexed element of every second pair -> 1/4 of the exponentials
-__device__ __forceinline__ float poly_exp2(float x) {
-  x = fmaxf(x, -126.f);
-  const float t = __fadd_rn(x, 12582912.f);   // 1.5 * 2^23: the integer part lands in the low mantissa bits
-  const float f = __fsub_rn(x, __fsub_rn(t, 12582912.f));
-  float p = fmaf(0.05592204f, f, 0.24264008f);
-  p = fmaf(p, f, 0.69312103f);
-  p = fmaf(p, f, 0.99992448f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
-
 enum Bar : int {
   kQFull = 0,                    // [2]  per query tile
   kKFull = 2,                    // [kStages]

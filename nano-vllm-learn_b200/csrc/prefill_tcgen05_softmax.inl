@@ -81,8 +81,7 @@
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const float p0 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i]), c, -m_sc));
-          const float p1 = (i & kPolyMask) ? poly_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i + 1]), c, -m_sc))
-                                           : fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i + 1]), c, -m_sc));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i + 1]), c, -m_sc));
           psum0 += p0;
           psum1 += p1;
           pk[i] = pack_bf16x2(p0, p1);
