@@ -88,6 +88,12 @@ __device__ __forceinline__ Item decode_item(const PrefillParams& p, int w, int n
 }
 
 
+// Debug-build timeline (tools/trace_prefill.py): CTA 0 stamps clock64() at the protocol points of its first
+// work item into debug[32768 + (role * 64 + step) * 8 + k]; role 0 = MMA issuer, 1 = softmax A, 2 = softmax B.
+__device__ __forceinline__ void trace_stamp(float* debug, int role, int step, int k) {
+  if (step < 64) reinterpret_cast<uint32_t*>(debug)[32768 + (role * 64 + step) * 8 + k] = static_cast<uint32_t>(clock64());
+}
+
 template <bool kDebug>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -133,11 +139,14 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 
   if (warp >= 8) {
     tc::reg_dealloc<96>();
-    if (warp == 8 && lane == 0) {
-      // ================================ TMA producer ================================
-      tc::tma_prefetch_desc(&tm_q);
-      tc::tma_prefetch_desc(&tm_k);
-      tc::tma_prefetch_desc(&tm_v);
+    if (warp == 8) {
+      // ================================ TMA producer (warp-wide, issue by one elected lane) ==========
+      const bool lead = tc::elect_one();
+      if (lead) {
+        tc::tma_prefetch_desc(&tm_q);
+        tc::tma_prefetch_desc(&tm_k);
+        tc::tma_prefetch_desc(&tm_v);
+      }
       uint32_t kv_iter = 0;        // K/V tiles loaded so far (ring position + phase)
       uint32_t q_uses[2] = {0, 0};  // how often Q_t has been filled
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
@@ -148,9 +157,12 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           tc::mbar_wait(bar(kQEmpty + t), (q_uses[t] & 1u) ^ 1u);
           ++q_uses[t];
           const uint32_t sq = smem + kSmemQ + t * kTileBytes;
-          tc::mbar_arrive_expect_tx(bar(kQFull + t), kTileBytes);
-          tc::tma_load_2d(sq, &tm_q, it.h * kHeadDim, it.q0 + it.m0 + t * TM, bar(kQFull + t));
-          tc::tma_load_2d(sq + kHalfBytes, &tm_q, it.h * kHeadDim + 64, it.q0 + it.m0 + t * TM, bar(kQFull + t));
+          if (lead) {
+            tc::mbar_arrive_expect_tx(bar(kQFull + t), kTileBytes);
+            tc::tma_load_2d(sq, &tm_q, it.h * kHeadDim, it.q0 + it.m0 + t * TM, bar(kQFull + t));
+            tc::tma_load_2d(sq + kHalfBytes, &tm_q, it.h * kHeadDim + 64, it.q0 + it.m0 + t * TM, bar(kQFull + t));
+          }
+          __syncwarp();
         }
         const int32_t* table =
             p.block_tables ? p.block_tables + static_cast<int64_t>(it.seq) * p.table_stride : nullptr;
@@ -166,16 +178,25 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           }
           const uint32_t sk = smem + kSmemK + st * kTileBytes;
           const uint32_t sv = smem + kSmemV + st * kTileBytes;
-          tc::mbar_arrive_expect_tx(bar(kKFull + st), kTileBytes);
-          tc::tma_load_2d(sk, &tm_k, it.kvh * kHeadDim, row, bar(kKFull + st));
-          tc::tma_load_2d(sk + kHalfBytes, &tm_k, it.kvh * kHeadDim + 64, row, bar(kKFull + st));
-          tc::mbar_arrive_expect_tx(bar(kVFull + st), kTileBytes);
-          tc::tma_load_2d(sv, &tm_v, it.kvh * kHeadDim, row, bar(kVFull + st));
-          tc::tma_load_2d(sv + kHalfBytes, &tm_v, it.kvh * kHeadDim + 64, row, bar(kVFull + st));
+          if (lead) {
+            tc::mbar_arrive_expect_tx(bar(kKFull + st), kTileBytes);
+            tc::tma_load_2d(sk, &tm_k, it.kvh * kHeadDim, row, bar(kKFull + st));
+            tc::tma_load_2d(sk + kHalfBytes, &tm_k, it.kvh * kHeadDim + 64, row, bar(kKFull + st));
+            tc::mbar_arrive_expect_tx(bar(kVFull + st), kTileBytes);
+            tc::tma_load_2d(sv, &tm_v, it.kvh * kHeadDim, row, bar(kVFull + st));
+            tc::tma_load_2d(sv + kHalfBytes, &tm_v, it.kvh * kHeadDim + 64, row, bar(kVFull + st));
+          }
+          __syncwarp();
         }
       }
-    } else if (warp == 9 && lane == 0) {
-      // ================================ MMA issuer ==================================
+    } else if (warp == 9) {
+      // ================================ MMA issuer (warp-wide, issue by one elected lane) ============
+      // Measured with clock64 stamps (tools/trace_prefill.py): run by a single divergent lane, every
+      // tcgen05.mma cost ~100-140 cycles of R2UR moves plus an ELECT/branch waterfall, i.e. the issue path,
+      // not the tensor pipe or the softmax, set the pace.  Warp-uniform control flow keeps descriptors in
+      // uniform registers.
+      const bool lead = tc::elect_one();
+      const uint64_t dq0 = tc::make_smem_desc(smem + kSmemQ, 16, 1024);
       uint32_t kv_base = 0;          // K/V tiles consumed by earlier items
       uint32_t q_uses[2] = {0, 0};   // items that used tile t (phase of q_full / o_empty)
       uint32_t p_cnt[2] = {0, 0};    // P tiles consumed per query tile (phase of p_full)
@@ -188,17 +209,22 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           if (j == 0) tc::mbar_wait(bar(kQFull + t), q_uses[t] & 1u);
           tc::mbar_wait(bar(kKFull + st), (kv / kStages) & 1u);
           tc::fence_after_sync();
-          const uint32_t sq = smem + kSmemQ + t * kTileBytes;
-          const uint32_t sk = smem + kSmemK + st * kTileBytes;
+          // descriptors differ only in the 14-bit start-address field (units of 16 B): add offsets to the low word
+          const uint64_t da = dq0 + static_cast<uint64_t>((t * kTileBytes) >> 4);
+          const uint64_t db = dq0 + static_cast<uint64_t>((kSmemK - kSmemQ + st * kTileBytes) >> 4);
           const uint32_t d = tmem + static_cast<uint32_t>(t * TN);
+          if (lead) {
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            const uint32_t off = (ks >> 2) * kHalfBytes + (ks & 3) * 32;  // 16 bf16 = 32 B inside the swizzle row
-            tc::mma_ss(d, tc::make_smem_desc(sq + off, 16, 1024), tc::make_smem_desc(sk + off, 16, 1024), kIdescQK,
-                       ks > 0 ? 1u : 0u);
+            for (int ks = 0; ks < 8; ++ks) {
+              // 16 bf16 = 32 B inside the swizzle row; dims 64..127 live in the second SW128 half
+              constexpr int kHalf16 = kHalfBytes >> 4;
+              const uint64_t off = static_cast<uint64_t>((ks >> 2) * kHalf16 + (ks & 3) * 2);
+              tc::mma_ss(d, da + off, db + off, kIdescQK, ks > 0 ? 1u : 0u);
+            }
+            tc::mma_commit(bar(kSFull + t));
+            if (j == it.n_t[t] - 1) tc::mma_commit(bar(kQEmpty + t));  // last read of Q_t for this item
           }
-          tc::mma_commit(bar(kSFull + t));
-          if (j == it.n_t[t] - 1) tc::mma_commit(bar(kQEmpty + t));  // last read of Q_t for this item
+          __syncwarp();
         };
         auto issue_pv = [&](int t, int j) {
           const uint32_t kv = kv_base + static_cast<uint32_t>(j);
@@ -208,25 +234,35 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           ++p_cnt[t];
           if (j == 0) tc::mbar_wait(bar(kOEmpty + t), (q_uses[t] & 1u) ^ 1u);  // previous item's epilogue drained O_t
           tc::fence_after_sync();
-          const uint32_t sv = smem + kSmemV + st * kTileBytes;
+          const uint64_t dv = tc::make_smem_desc(smem + kSmemV + st * kTileBytes, kHalfBytes, 1024);
           const uint32_t d = tmem + 2u * TN + static_cast<uint32_t>(t * kHeadDim);
           const uint32_t a = tmem + static_cast<uint32_t>(t * TN);
+          if (lead) {
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            // 16 keys = 16 rows of 128 B per k-step; the two 64-dim halves are kHalfBytes apart (LBO)
-            tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), tc::make_smem_desc(sv + ks * 2048, kHalfBytes, 1024),
-                       kIdescPV, (j > 0 || ks > 0) ? 1u : 0u);
+            for (int ks = 0; ks < 8; ++ks) {
+              // 16 keys = 16 rows of 128 B per k-step (2048 B = 128 x 16 B); the two 64-dim halves are LBO apart
+              tc::mma_ts(d, a + static_cast<uint32_t>(ks * 8), dv + static_cast<uint64_t>(ks * 128), kIdescPV,
+                         (j > 0 || ks > 0) ? 1u : 0u);
+            }
+            tc::mma_commit(bar(kOFull + t));
           }
-          tc::mma_commit(bar(kOFull + t));
+          __syncwarp();
         };
         for (int t = 0; t < 2; ++t)
           if (it.n_t[t] > 0) issue_qk(t, 0);
+        const bool tr = kDebug && lead && debug != nullptr && blockIdx.x == 0 && w == static_cast<int>(blockIdx.x);
         for (int j = 0; j < it.n_tiles; ++j) {
+          if (tr) trace_stamp(debug, 0, j, 0);
           if (j < it.n_t[0]) issue_pv(0, j);
+          if (tr) trace_stamp(debug, 0, j, 1);
           if (j + 1 < it.n_t[0]) issue_qk(0, j + 1);
+          if (tr) trace_stamp(debug, 0, j, 2);
           if (j < it.n_t[1]) issue_pv(1, j);
-          tc::mma_commit(bar(kKVEmpty + (kv_base + j) % kStages));  // K_j, V_j no longer read by any pending MMA
+          if (tr) trace_stamp(debug, 0, j, 3);
+          if (lead) tc::mma_commit(bar(kKVEmpty + (kv_base + j) % kStages));  // K_j, V_j no longer read by any pending MMA
+          __syncwarp();
           if (j + 1 < it.n_t[1]) issue_qk(1, j + 1);
+          if (tr) trace_stamp(debug, 0, j, 4);
         }
         kv_base += static_cast<uint32_t>(it.n_tiles);
         for (int t = 0; t < 2; ++t)

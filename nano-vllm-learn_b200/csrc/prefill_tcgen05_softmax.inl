@@ -20,15 +20,19 @@
     float m_used = -INFINITY;  // max the stored P/O/l are relative to (may lag the true max by < 2^8)
     float l_run = 0.f;
 
+    const bool tr = kDebug && debug != nullptr && blockIdx.x == 0 && w == static_cast<int>(blockIdx.x) && row == 0;
     for (int j = 0; j < nt; ++j) {
       const int t_base = j * TN;
+      if (tr) trace_stamp(debug, 1 + t, j, 0);
       tc::mbar_wait(bar(kSFull + t), s_cnt & 1u);
       ++s_cnt;
       tc::fence_after_sync();
+      if (tr) trace_stamp(debug, 1 + t, j, 1);
       uint32_t s[TN];
 #pragma unroll
       for (int cc = 0; cc < 4; ++cc) tc::tmem_ld32p(s_addr + cc * 32, s + cc * 32);
       tc::tmem_ld_wait();
+      if (tr) trace_stamp(debug, 1 + t, j, 2);
       if (dump && j == 0) {
 #pragma unroll
         for (int i = 0; i < TN; ++i) debug[row * TN + i] = __uint_as_float(s[i]);
@@ -73,6 +77,7 @@
           }
         }
       }
+      if (tr) trace_stamp(debug, 1 + t, j, 3);
       const float m_sc = (m_used == -INFINITY) ? 0.f : m_used * c;
       float psum0 = 0.f, psum1 = 0.f;
 #pragma unroll
@@ -88,9 +93,11 @@
         }
         tc::tmem_st16(s_addr + cc * 16, pk);
       }
+      if (tr) trace_stamp(debug, 1 + t, j, 4);
       tc::tmem_st_wait();
       tc::fence_before_sync();
       tc::mbar_arrive(bar(kPFull + t));
+      if (tr) trace_stamp(debug, 1 + t, j, 5);
       l_run += psum0 + psum1;
     }
 
