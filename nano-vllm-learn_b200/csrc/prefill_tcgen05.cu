@@ -136,6 +136,10 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
+  // debug build only: bit0 = softmax skips exp2 + P stores, bit1 = also skips the S loads, bit2 = the producer
+  // arrives on K/V barriers without loading (tools/trace_prefill.py uses these to time the MMA pipe alone)
+  const uint32_t dbg_mode =
+      (kDebug && debug != nullptr) ? reinterpret_cast<const uint32_t*>(debug)[32768 + 3 * 64 * 8] : 0u;
 
   if (warp >= 8) {
     tc::reg_dealloc<96>();
@@ -178,7 +182,10 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           }
           const uint32_t sk = smem + kSmemK + st * kTileBytes;
           const uint32_t sv = smem + kSmemV + st * kTileBytes;
-          if (lead) {
+          if (lead && (dbg_mode & 4u)) {
+            tc::mbar_arrive(bar(kKFull + st));
+            tc::mbar_arrive(bar(kVFull + st));
+          } else if (lead) {
             tc::mbar_arrive_expect_tx(bar(kKFull + st), kTileBytes);
             tc::tma_load_2d(sk, &tm_k, it.kvh * kHeadDim, row, bar(kKFull + st));
             tc::tma_load_2d(sk + kHalfBytes, &tm_k, it.kvh * kHeadDim + 64, row, bar(kKFull + st));
@@ -213,7 +220,29 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           const uint64_t da = dq0 + static_cast<uint64_t>((t * kTileBytes) >> 4);
           const uint64_t db = dq0 + static_cast<uint64_t>((kSmemK - kSmemQ + st * kTileBytes) >> 4);
           const uint32_t d = tmem + static_cast<uint32_t>(t * TN);
-          if (lead) {
+          if (kDebug && (dbg_mode & 24u)) {
+            // timing experiments only (results are garbage): bit3 = alternate two accumulators, bit4 = N=256
+            if (lead) {
+              constexpr int kHalf16 = kHalfBytes >> 4;
+              if (dbg_mode & 8u) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                  const uint64_t off = static_cast<uint64_t>((ks >> 2) * kHalf16 + (ks & 3) * 2);
+                  const uint32_t dd = (ks & 1) ? tmem + 2u * TN + static_cast<uint32_t>(t * kHeadDim) : d;
+                  tc::mma_ss(dd, da + off, db + off, kIdescQK, ks > 1 ? 1u : 0u);
+                }
+              } else {
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                  const uint64_t off = static_cast<uint64_t>((ks >> 2) * kHalf16 + (ks & 3) * 2);
+                  tc::mma_ss(tmem + static_cast<uint32_t>(t * 2 * TN), da + off, db + off,
+                             tc::make_idesc_bf16(TM, 256, false), ks > 0 ? 1u : 0u);
+                }
+              }
+              tc::mma_commit(bar(kSFull + t));
+              if (j == it.n_t[t] - 1) tc::mma_commit(bar(kQEmpty + t));
+            }
+          } else if (lead) {
 #pragma unroll
             for (int ks = 0; ks < 8; ++ks) {
               // 16 bf16 = 32 B inside the swizzle row; dims 64..127 live in the second SW128 half

@@ -29,9 +29,14 @@
       tc::fence_after_sync();
       if (tr) trace_stamp(debug, 1 + t, j, 1);
       uint32_t s[TN];
+      if (dbg_mode & 2u) {
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) tc::tmem_ld32p(s_addr + cc * 32, s + cc * 32);
-      tc::tmem_ld_wait();
+        for (int i = 0; i < TN; ++i) s[i] = 0u;
+      } else {
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) tc::tmem_ld32p(s_addr + cc * 32, s + cc * 32);
+        tc::tmem_ld_wait();
+      }
       if (tr) trace_stamp(debug, 1 + t, j, 2);
       if (dump && j == 0) {
 #pragma unroll
@@ -80,18 +85,20 @@
       if (tr) trace_stamp(debug, 1 + t, j, 3);
       const float m_sc = (m_used == -INFINITY) ? 0.f : m_used * c;
       float psum0 = 0.f, psum1 = 0.f;
+      if (!(dbg_mode & 1u)) {
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) {
-        uint32_t pk[16];
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i]), c, -m_sc));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i + 1]), c, -m_sc));
-          psum0 += p0;
-          psum1 += p1;
-          pk[i] = pack_bf16x2(p0, p1);
+          for (int i = 0; i < 16; ++i) {
+            const float p0 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i]), c, -m_sc));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(s[cc * 32 + 2 * i + 1]), c, -m_sc));
+            psum0 += p0;
+            psum1 += p1;
+            pk[i] = pack_bf16x2(p0, p1);
+          }
+          tc::tmem_st16(s_addr + cc * 16, pk);
         }
-        tc::tmem_st16(s_addr + cc * 16, pk);
       }
       if (tr) trace_stamp(debug, 1 + t, j, 4);
       tc::tmem_st_wait();
