@@ -20,6 +20,7 @@
  *                              (flash_attn_varlen_func(..., causal=True,
  *                               block_table=...)); no-prefix semantics:
  *                              nanovllm/layers/attention_sdpa.py:65-119
+ *   nvllm_sample_tokens     <- nanovllm/layers/sampler.py:10-18 (Sampler.forward)
  *   nvllm_prepare_decode / nvllm_prepare_prefill_slots
  *                           <- nanovllm/engine/model_runner.py:244-269 and
  *                              :212-221 (index math of the runner glue)
@@ -249,6 +250,36 @@ NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
                                     int32_t num_cached_tokens,
                                     int32_t block_size, int32_t* slots_out,
                                     int64_t capacity);
+
+/* ------------------------------------------------------------------------
+ * (5) fused token sampler (SURVEY §8f "next", rank 4): one launch for the
+ *     whole of Sampler.forward.
+ *     reference: nanovllm/layers/sampler.py:10-18, called from
+ *                nanovllm/engine/model_runner.py:311
+ *
+ *   greedy_b  = argmax_i float(logits[b, i])   (ties -> lowest index, NaN
+ *               greatest: torch.argmax ordering)
+ *   sampled_b = argmax_i softmax(logits[b,:] / T_b)[i] / (E[b,i] + 1e-10)
+ *             = argmax_i (logits[b,i] / T_b - ln(E[b,i] + 1e-10))
+ *   tokens_out[b] = T_b == 0 ? greedy_b : sampled_b            (int64)
+ *
+ *   logits [bs, vocab], logits_elem_bytes 2 (bf16) or 4 (fp32), row stride in
+ *   elements; 16-byte aligned rows take the vector path, others a scalar one.
+ *   noise != NULL: E is read from this fp32 [bs, vocab] tensor (the parity
+ *   tests inject the reference's own exponential_ draw).  noise == NULL:
+ *   E[b,i] = -ln(u), u from Philox4x32-10 with key = seed and counter =
+ *   (i / 4, b, offset); word i % 4 of the block, top 24 bits, u = (w + 0.5) / 2^24.
+ *   workspace: nvllm_sample_workspace_bytes(bs) bytes, 16-byte aligned,
+ *   ZERO-FILLED ONCE before first use (self-resetting arrival counters), not
+ *   shared by concurrent launches.  bs <= 4096.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_sample_tokens(int64_t* tokens_out, const void* logits,
+                        int32_t logits_elem_bytes, int64_t logits_row_stride,
+                        const float* temperatures, const float* noise,
+                        int64_t noise_row_stride, int32_t bs, int32_t vocab,
+                        uint64_t seed, uint64_t offset, void* workspace,
+                        size_t workspace_bytes, void* stream);
+NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
 
 /* Measurement aid (tools/membench.py), not on the product path: streams `bytes`
  * of `buf` with contiguous warp reads (pattern 0) or with the decode kernel's

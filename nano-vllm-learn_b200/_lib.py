@@ -3,7 +3,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint64, c_void_p
 from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
@@ -35,6 +35,9 @@ SIGNATURES = {
     "nvllm_qk_norm_rope_store": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                          c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
                                          c_int32, c_int32, c_void_p]),
+    "nvllm_sample_tokens": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32, c_int32,
+                                    c_uint64, c_uint64, c_void_p, c_size_t, c_void_p]),
+    "nvllm_sample_workspace_bytes": (c_size_t, [c_int32]),
     "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),

@@ -229,3 +229,38 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
                                   block_size, float(softmax_scale), _stream())
     _lib.check(st, "varlen_prefill")
     return out
+
+
+# Sampler workspace (arrival counters + chunk partials), one per device, zero-filled once.
+_SAMPLE_WS: dict[int, torch.Tensor] = {}
+
+
+def sample_tokens(logits: torch.Tensor, temperatures: torch.Tensor, noise: Optional[torch.Tensor] = None,
+                  seed: int = 0, offset: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused Sampler.forward (nanovllm/layers/sampler.py:10-18): logits [bs, vocab] bf16/fp32, temperatures [bs]
+    fp32 -> int64 token ids [bs].  `noise` (fp32 [bs, vocab], Exp(1) draws) replaces the in-kernel Philox stream."""
+    lib = _lib.load()
+    _require_cuda(logits, temperatures, noise)
+    assert logits.dim() == 2 and logits.stride(1) == 1
+    assert logits.dtype in (torch.bfloat16, torch.float32)
+    bs, vocab = logits.shape
+    assert temperatures.dtype == torch.float32 and temperatures.numel() == bs and temperatures.is_contiguous()
+    if noise is not None:
+        assert noise.dtype == torch.float32 and noise.shape == logits.shape and noise.stride(1) == 1
+    if out is None:
+        out = torch.empty(bs, dtype=torch.int64, device=logits.device)
+    if bs == 0:
+        return out
+    idx = logits.device.index if logits.device.index is not None else torch.cuda.current_device()
+    need = int(lib.nvllm_sample_workspace_bytes(bs))
+    ws = _SAMPLE_WS.get(idx)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=logits.device)
+        _SAMPLE_WS[idx] = ws
+    st = lib.nvllm_sample_tokens(out.data_ptr(), logits.data_ptr(), logits.element_size(), logits.stride(0),
+                                 temperatures.data_ptr(), noise.data_ptr() if noise is not None else None,
+                                 noise.stride(0) if noise is not None else 0, bs, vocab,
+                                 seed & 0xFFFFFFFFFFFFFFFF, offset & 0xFFFFFFFFFFFFFFFF, ws.data_ptr(), ws.numel(),
+                                 _stream())
+    _lib.check(st, "sample_tokens")
+    return out

@@ -157,3 +157,27 @@ def rope_cache(base: float, max_position: int):
     t = torch.arange(max_position, dtype=torch.float)
     freqs = torch.einsum("i,j -> ij", t, inv_freq)
     return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
+
+
+# name -> (seed, bs, vocab, dtype, temperatures)   token sampler (reference sampler.py)
+SAMPLER_CASES = {
+    "s_greedy_bf16": (40, 5, 151936, torch.bfloat16, [0.0, 0.0, 0.0, 0.0, 0.0]),
+    "s_mixed_bf16": (41, 6, 4099, torch.bfloat16, [0.0, 0.7, 1.0, 0.0, 1.3, 0.5]),
+    "s_mixed_fp32": (42, 4, 1000, torch.float32, [1.0, 0.0, 0.25, 2.0]),
+    "s_peaked": (43, 8, 2048, torch.bfloat16, [0.6] * 8),
+}
+
+
+def make_sampler_case(name: str):
+    """Logits with deliberate exact ties at the maximum (bf16 rounding makes them common anyway); `s_peaked`
+    scales the logits so the sampled token is not always the noise's favourite."""
+    seed, bs, vocab, dtype, temps = SAMPLER_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(bs, vocab, generator=g) * (6.0 if name == "s_peaked" else 2.0)
+    logits = logits.to(dtype)
+    # rows 0 and 1: the row maximum appears three times; the lowest index must win
+    for r in range(min(2, bs)):
+        top = logits[r].float().max().to(dtype)
+        idx = torch.randint(0, vocab, (3,), generator=g)
+        logits[r, idx] = top
+    return dict(logits=logits, temperatures=torch.tensor(temps, dtype=torch.float32), noise_seed=1000 + seed)

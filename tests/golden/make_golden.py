@@ -170,8 +170,28 @@ def gen_pre_attention():
     print("pre_attention", tuple(qr.shape), tuple(kr.shape))
 
 
+def gen_sampler():
+    """nanovllm/layers/sampler.py::Sampler.forward, the reference class itself on CPU; its exponential_ draw is
+    the first use of torch's CPU generator after torch.manual_seed(noise_seed)."""
+    from oracle.sampler_oracle import load_reference_sampler
+    ref = load_reference_sampler((REF,))()
+    outs = {}
+    for name in cases.SAMPLER_CASES:
+        c = cases.make_sampler_case(name)
+        torch.manual_seed(c["noise_seed"])
+        with torch.no_grad():
+            tok = ref(c["logits"].clone(), c["temperatures"])
+        outs[f"{name}_tokens"] = tok.numpy()
+        outs[f"{name}_sha"] = cases.sha(c["logits"], c["temperatures"])
+        print("sampler", name, tok.tolist())
+    np.savez_compressed(os.path.join(HERE, "sampler.npz"), meta=json.dumps(META), **outs)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--sampler-only" in sys.argv:
+        gen_sampler()
+        sys.exit(0)
     if "--pre-attention-only" in sys.argv:
         gen_pre_attention()
         sys.exit(0)
@@ -180,3 +200,4 @@ if __name__ == "__main__":
     gen_gather()
     gen_glue()
     gen_pre_attention()
+    gen_sampler()

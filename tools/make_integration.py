@@ -3,7 +3,7 @@
     python tools/make_integration.py [--src baseline/_ref] [--dst build/nanovllm_cuda]
 
 Copies `<src>/nanovllm` to `<dst>/nanovllm` (git-ignored, never committed) and applies exactly the
-edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusion A5), plus two environment-compat
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5/A6), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
 anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
@@ -41,6 +41,14 @@ EDITS = [
      '        qkv = self.qkv_proj(hidden_states)\n'
      '        if self.attn_backend == "cuda" and __import__("os").environ.get("NVLLM_FUSED_PRE_ATTN", "1") != "0":\n'
      '            return self.o_proj(self.attn.forward_fused(qkv, positions, self.q_norm, self.k_norm, self.rotary_emb))\n'),
+    # ---- A6 (optional: NVLLM_FUSED_SAMPLER=0 keeps the reference's eager sampler):
+    #      one fused kernel for Sampler.forward (nanovllm/engine/model_runner.py:38, nanovllm/layers/sampler.py:10-18)
+    ("nanovllm/engine/model_runner.py",
+     '        self.sampler = Sampler()\n',
+     '        self.sampler = Sampler()\n'
+     '        if attn_backend == "cuda" and __import__("os").environ.get("NVLLM_FUSED_SAMPLER", "1") != "0":\n'
+     '            from nano_vllm_learn_b200.sampler_cuda import Sampler as _CudaSampler\n'
+     '            self.sampler = _CudaSampler()\n'),
     # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
     ("nanovllm/config.py",
      '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',
