@@ -24,8 +24,14 @@ def _run(backend, model_dir, prompts, steps, port):
     rec = {}
     try:
         runner = llm.model_runner
+        installed = runner.sampler
+        rec["sampler_type"] = type(installed).__module__
 
         def fixed_sampler(logits, temperatures):
+            if backend == "cuda":
+                # edit A6 in situ: the fused sampler the engine installed vs the reference module, same logits
+                from nanovllm.layers.sampler import Sampler as RefSampler
+                assert torch.equal(installed(logits, temperatures), RefSampler()(logits.clone(), temperatures))
             rec["logits"] = logits.float().cpu()
             n = rec.get("calls", 0)
             rec["calls"] = n + 1
@@ -79,6 +85,7 @@ def test_engine_flash_vs_cuda(tmp_path, fused):
     b = _run("cuda", model_dir, prompts, steps, 2392)
     assert a["tokens"] == b["tokens"]                      # the pinned sampler ran the same number of steps
     assert a["calls"] == b["calls"] == steps
+    assert b["sampler_type"].endswith("sampler_cuda") and a["sampler_type"] == "nanovllm.layers.sampler"   # edit A6
     ka, kb = a["kv"], b["kv"]
     # layer 0: bit-exact (store kernel + glue slot mapping in situ); V always, K when the reference's own
     # norm/rope kernels produced it
