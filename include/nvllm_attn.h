@@ -267,8 +267,12 @@ NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
  *   elements; 16-byte aligned rows take the vector path, others a scalar one.
  *   noise != NULL: E is read from this fp32 [bs, vocab] tensor (the parity
  *   tests inject the reference's own exponential_ draw).  noise == NULL:
- *   E[b,i] = -ln(u), u from Philox4x32-10 with key = seed and counter =
- *   (i / 4, b, offset); word i % 4 of the block, top 24 bits, u = (w + 0.5) / 2^24.
+ *   E[b,i] = -ln(1 - m), m = (w >> 9) / 2^23, w = word i % 4 of the Philox4x32-10
+ *   block with key = seed and counter = (i / 4, b, offset).  Elements whose
+ *   logit cannot reach the running best key even with the largest possible
+ *   noise term (-ln(1e-10)) are skipped without drawing their noise.
+ *   Rows holding NaN or +inf logits with T != 0 are outside the contract (the
+ *   reference's softmax turns such a row into NaN and answers token 0).
  *   workspace: nvllm_sample_workspace_bytes(bs) bytes, 16-byte aligned,
  *   ZERO-FILLED ONCE before first use (self-resetting arrival counters), not
  *   shared by concurrent launches.  bs <= 4096.

@@ -64,8 +64,15 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
   }
   return c;
 }
-// 24 random bits -> uniform in (0, 1): never 0 (ln stays finite) and never 1
-__device__ __forceinline__ float u01(uint32_t x) { return (static_cast<float>(x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+// 23 random bits -> m uniform on [0, 1) (exact multiples of 2^-23), E = -ln(1 - m) ~ Exp(1) on [0, 15.95].
+// Small m goes through the series m + m^2/2 + m^3/3 so that E keeps RELATIVE accuracy where the second
+// logarithm, -ln(E + eps), is steep (lg2.approx alone has ~2^-22 absolute error near 1).
+__device__ __forceinline__ float exp1_from_bits(uint32_t w) {
+  const float m = __uint_as_float((w >> 9) | 0x3F800000u) - 1.0f;
+  const float series = m * fmaf(m, fmaf(m, 0.33333334f, 0.5f), 1.0f);
+  const float lg = -0.6931471805599453f * fast_log2(1.0f - m);
+  return m < 0.015625f ? series : lg;
+}
 
 struct SampleParams {
   const void* logits;
@@ -87,56 +94,147 @@ __device__ __forceinline__ float to_f32<float>(float x) { return x; }
 template <>
 __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 x) { return __bfloat162float(x); }
 
-// kVec elements per thread per trip: 8 bf16 or 4 fp32 = one 16-byte load.
+// One 16-byte vector (8 bf16 / 4 fp32) of a row, raw; lanes at or beyond `end` read as -inf.
 template <typename T, bool kAligned>
-__global__ void __launch_bounds__(kSampleThreads) sample_tokens_kernel(const SampleParams p) {
+__device__ __forceinline__ uint4 load_raw(const T* lrow, int i0, int end) {
   constexpr int kVec = 16 / sizeof(T);
+  uint4 raw;
+  if (kAligned && i0 + kVec <= end) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w)
+                 : "l"(lrow + i0));
+  } else {
+    T* e = reinterpret_cast<T*>(&raw);
+#pragma unroll
+    for (int k = 0; k < kVec; ++k) e[k] = (i0 + k < end) ? lrow[i0 + k] : static_cast<T>(-INFINITY);
+  }
+  return raw;
+}
+template <typename T>
+__device__ __forceinline__ void unpack(const uint4& raw, float (&x)[16 / sizeof(T)]) {
+  const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+  for (int k = 0; k < 16 / sizeof(T); ++k) x[k] = to_f32<T>(e[k]);
+}
+
+__device__ __forceinline__ float max_nan_f32(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;\n" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t max_nan_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("max.NaN.bf16x2 %0, %1, %2;\n" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+// Largest element of a vector, NaN if it holds one (torch.argmax ranks NaN above everything).
+template <typename T>
+__device__ __forceinline__ float vec_max(const uint4& raw);
+template <>
+__device__ __forceinline__ float vec_max<float>(const uint4& r) {
+  return max_nan_f32(max_nan_f32(__uint_as_float(r.x), __uint_as_float(r.y)),
+                     max_nan_f32(__uint_as_float(r.z), __uint_as_float(r.w)));
+}
+template <>
+__device__ __forceinline__ float vec_max<__nv_bfloat16>(const uint4& r) {
+  const uint32_t m = max_nan_bf16x2(max_nan_bf16x2(r.x, r.y), max_nan_bf16x2(r.z, r.w));
+  return max_nan_f32(__uint_as_float(m << 16), __uint_as_float(m & 0xffff0000u));
+}
+
+// An element can only win the sampled argmax if logit/T + Gmax beats the best key so far, Gmax = -ln(eps) =
+// 23.03 being the largest noise term there is.  In the logit domain: logit > (best - Gmax) * T.  Slack covers
+// the roundings; NaN (temperature < 0, or a NaN/inf best) disables skipping because !(x <= NaN) holds.
+__device__ __forceinline__ float skip_threshold(float best_key, float temp) {
+  if (!(temp > 0.f)) return __int_as_float(0x7fc00000);
+  const float k = best_key - 23.1f - fabsf(best_key) * 9.5367431640625e-7f;
+  const float t = k * temp;
+  return t - fabsf(t) * 9.5367431640625e-7f;
+}
+
+constexpr int kUnroll = 4;   // 16-byte loads in flight per thread
+
+// kVec elements per thread per load: 8 bf16 or 4 fp32.
+template <typename T, bool kAligned>
+__global__ void __launch_bounds__(kSampleThreads, 4) sample_tokens_kernel(const SampleParams p) {
+  constexpr int kVec = 16 / sizeof(T);
+  constexpr int kStride = kSampleThreads * kVec;
   const int row = blockIdx.y;
   const int chunk = blockIdx.x;
   const int tid = threadIdx.x;
   const T* lrow = static_cast<const T*>(p.logits) + static_cast<int64_t>(row) * p.row_stride;
   const float temp = __ldg(p.temperatures + row);
   const bool sample = temp != 0.f;
+  const float inv_t = __frcp_rn(temp);
   const float* nrow = p.noise ? p.noise + static_cast<int64_t>(row) * p.noise_row_stride : nullptr;
   const int begin = chunk * p.chunk_elems;
   const int end = min(p.vocab, begin + p.chunk_elems);
+  const uint2 key = make_uint2(p.seed_lo, p.seed_hi);
 
+  // a row needs only one of the two criteria: greedy (T == 0) or sampled
   Cand g = {-INFINITY, INT_MAX}, s = {-INFINITY, INT_MAX};
-  for (int i0 = begin + tid * kVec; i0 < end; i0 += kSampleThreads * kVec) {
-    float x[kVec];
-    if (kAligned && i0 + kVec <= end) {
-      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(lrow + i0));
-      const T* e = reinterpret_cast<const T*>(&raw);
+  if (!sample) {
+    // Greedy: ~1 instruction per element.  Track the best VECTOR (its maximum and where it starts); vectors are
+    // visited in rising index order, so a later vector replaces the best one only when strictly greater (or the
+    // first to hold a NaN).  The winning vector is re-read once at the end to find the element.
+    float best = -INFINITY;
+    int best_i0 = -1;
+    for (int base = begin + tid * kVec; base < end; base += kUnroll * kStride) {
+      uint4 raw[kUnroll];
 #pragma unroll
-      for (int k = 0; k < kVec; ++k) x[k] = to_f32<T>(e[k]);
-    } else {
+      for (int u = 0; u < kUnroll; ++u) raw[u] = load_raw<T, kAligned>(lrow, base + u * kStride, end);
 #pragma unroll
-      for (int k = 0; k < kVec; ++k) x[k] = (i0 + k < end) ? to_f32<T>(lrow[i0 + k]) : -INFINITY;
-    }
-#pragma unroll
-    for (int k = 0; k < kVec; ++k)
-      if (i0 + k < end) take(g, x[k], i0 + k);
-    if (sample) {
-      float e[kVec];
-      if (nrow) {
-#pragma unroll
-        for (int k = 0; k < kVec; ++k) e[k] = (i0 + k < end) ? __ldg(nrow + i0 + k) : 1.f;
-      } else {
-        // one Philox block per 4 consecutive elements: counter = (element group, row, offset)
-#pragma unroll
-        for (int k = 0; k < kVec; k += 4) {
-          const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>((i0 + k) >> 2), static_cast<uint32_t>(row),
-                                                   p.off_lo, p.off_hi),
-                                        make_uint2(p.seed_lo, p.seed_hi));
-          e[k + 0] = -logf(u01(r.x));
-          e[k + 1] = -logf(u01(r.y));
-          e[k + 2] = -logf(u01(r.z));
-          e[k + 3] = -logf(u01(r.w));
-        }
+      for (int u = 0; u < kUnroll; ++u) {
+        const float m = vec_max<T>(raw[u]);
+        const bool upd = (m > best) || ((m != m) && (best == best));
+        best = upd ? m : best;
+        best_i0 = upd ? base + u * kStride : best_i0;
       }
+    }
+    if (best_i0 >= 0) {
+      float x[kVec];
+      unpack<T>(load_raw<T, kAligned>(lrow, best_i0, end), x);
 #pragma unroll
-      for (int k = 0; k < kVec; ++k)
-        if (i0 + k < end) take(s, __fdiv_rn(x[k], temp) - logf(e[k] + kNoiseEps), i0 + k);   // IEEE divide, as logits.div_(T)
+      for (int k = kVec - 1; k >= 0; --k)
+        if (best_i0 + k < end && (x[k] == best || (best != best && x[k] != x[k]))) g = Cand{x[k], best_i0 + k};
+    }
+  } else {
+    float thr = skip_threshold(-INFINITY, temp);
+    for (int base = begin + tid * kVec; base < end; base += kUnroll * kStride) {
+      uint4 raw[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) raw[u] = load_raw<T, kAligned>(lrow, base + u * kStride, end);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i0 = base + u * kStride;
+        if (i0 >= end || vec_max<T>(raw[u]) <= thr) continue;   // nothing in this vector can win
+        float x[kVec], e[kVec];
+        unpack<T>(raw[u], x);
+        if (nrow) {
+#pragma unroll
+          for (int k = 0; k < kVec; ++k) e[k] = (i0 + k < end) ? __ldg(nrow + i0 + k) : 1.f;
+        } else {
+          // one Philox block per 4 consecutive elements: counter = (element group, row, offset)
+#pragma unroll
+          for (int k = 0; k < kVec; k += 4) {
+            const uint4 r = philox4x32_10(
+                make_uint4(static_cast<uint32_t>((i0 + k) >> 2), static_cast<uint32_t>(row), p.off_lo, p.off_hi), key);
+            e[k + 0] = exp1_from_bits(r.x);
+            e[k + 1] = exp1_from_bits(r.y);
+            e[k + 2] = exp1_from_bits(r.z);
+            e[k + 3] = exp1_from_bits(r.w);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kVec; ++k) {
+          // logit / T - ln(E + eps); the quotient as a product with the correctly rounded reciprocal.  Indices
+          // rise along the walk, so strictly-greater keeps the lowest index among equal keys.
+          const float kv = fmaf(-0.6931471805599453f, fast_log2(e[k] + kNoiseEps), x[k] * inv_t);
+          const bool upd = (i0 + k < end) && (kv > s.v);
+          s.v = upd ? kv : s.v;
+          s.i = upd ? i0 + k : s.i;
+        }
+        thr = skip_threshold(s.v, temp);
+      }
     }
   }
 
@@ -178,7 +276,7 @@ __global__ void __launch_bounds__(kSampleThreads) sample_tokens_kernel(const Sam
   warp_best(s);
   if (tid == 0) {
     int tok = sample ? s.i : g.i;
-    if (tok == INT_MAX) tok = 0;   // a row of -inf sample keys (all-NaN keys cannot lose to the sentinel)
+    if (tok == INT_MAX) tok = 0;   // a row whose every key is -inf: torch.argmax answers 0
     p.tokens[row] = static_cast<int64_t>(tok);
   }
 }
@@ -212,8 +310,9 @@ extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int3
     sms = v;
   }
   const int vec = 16 / logits_elem_bytes;
-  // about four CTAs per SM across the batch; a chunk is a whole number of 16-byte vectors per thread trip
-  int chunks = (4 * sms + bs - 1) / bs;
+  // one resident wave (__launch_bounds__ guarantees four CTAs per SM) split across the batch, never 1.x waves;
+  // a chunk is a whole number of 16-byte vectors
+  int chunks = (4 * sms) / bs;
   chunks = chunks < 1 ? 1 : (chunks > kMaxChunks ? kMaxChunks : chunks);
   int chunk_elems = (vocab + chunks - 1) / chunks;
   chunk_elems = (chunk_elems + vec - 1) / vec * vec;

@@ -51,6 +51,8 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--vocab", type=int, default=151936)
     ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--dist", choices=["normal3", "peaked"], default="normal3")
+    ap.add_argument("--bs", type=int, nargs="*", default=[1, 8, 16, 64, 256, 512])
     args = ap.parse_args()
     from nano_vllm_learn_b200.sampler_cuda import Sampler
     ref_cls = load_reference_sampler()
@@ -61,18 +63,24 @@ def main():
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     hbm = float(peaks.get("hbm_gbs", 6551.0))
     lines = []
-    for bs in (1, 8, 16, 64, 256, 512):
+    for bs in args.bs:
         nbytes = bs * args.vocab * 2
         n_pool = max(2, min(64, (256 << 20) // nbytes + 1))
         g = torch.Generator(device=dev).manual_seed(bs)
         pool = [(torch.randn(bs, args.vocab, generator=g, device=dev) * 3).to(torch.bfloat16) for _ in range(n_pool)]
+        if args.dist == "peaked":
+            # closer to a trained model's logits: a narrow bulk and a few dozen tokens far above it
+            for x in pool:
+                x.mul_(0.5)
+                idx = torch.randint(0, args.vocab, (bs, 32), generator=g, device=dev)
+                x.scatter_(1, idx, (14 + 8 * torch.rand(bs, 32, generator=g, device=dev)).to(torch.bfloat16))
         for temp in (0.0, 0.8):
             t = torch.full((bs,), temp, device=dev)
             us_mine = timed(lambda x: mine(x, t), pool, args.iters)
             us_ref = timed(lambda x: ref(x, t), pool, args.iters) if ref is not None else None
             if temp == 0.0 and ref is not None:
                 assert torch.equal(mine(pool[0], t), ref(pool[0].clone(), t))
-            line = dict(bs=bs, vocab=args.vocab, temperature=temp, fused_us=round(us_mine, 2),
+            line = dict(bs=bs, vocab=args.vocab, dist=args.dist, temperature=temp, fused_us=round(us_mine, 2),
                         reference_us=None if us_ref is None else round(us_ref, 2),
                         speedup=None if us_ref is None else round(us_ref / us_mine, 2),
                         algorithmic_bytes=nbytes + bs * 12,
