@@ -285,6 +285,72 @@ NVLLM_API int nvllm_sample_tokens(int64_t* tokens_out, const void* logits,
                         size_t workspace_bytes, void* stream);
 NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
 
+/* ------------------------------------------------------------------------
+ * (6) fused RowParallelLinear (SURVEY §8f "next", rank 2): the o_proj /
+ *     down_proj GEMM and the tensor-parallel all-reduce that follows it, in
+ *     ONE launch per rank over NVLink peer memory.
+ *     reference: nanovllm/layers/linear.py:158-190 (RowParallelLinear:
+ *                y = F.linear(x, W_r, bias if rank 0); dist.all_reduce(y)),
+ *                call sites nanovllm/models/qwen3.py:118 (o_proj), :147
+ *                (down_proj); process group: engine/model_runner.py:31.
+ *
+ *   y[n, out] = bf16( sum_r sum_k x_r[n, k] * W_r[out, k]  (+ bias[out]) )
+ *   with fp32 accumulation and a single rounding; every rank receives the
+ *   bit-identical y.  x_r [n_tokens, in_features_per_rank] and W_r
+ *   [out_features, in_features_per_rank] are this rank's bf16 shards (row
+ *   strides in elements, rows 16-byte aligned), bias bf16 [out_features] or
+ *   NULL (pass the same values on every rank: it is added once, after the
+ *   reduction).  1 <= n_tokens <= 512 (decode and short prefill; larger
+ *   batches are GEMM-bound and keep the reference's cuBLAS + NCCL path),
+ *   in_features_per_rank % 64 == 0, out_features % 64 == 0, 2 <= world <= 8.
+ *
+ *   Communicator: every rank owns ONE buffer of nvllm_rowparallel_comm_bytes()
+ *   bytes, obtained from nvllm_tp_comm_alloc (cudaMalloc + zeroed control
+ *   area + a 64-byte CUDA IPC handle to hand to the peer processes, e.g. via
+ *   torch.distributed.all_gather_object) and mapped by the peers with
+ *   nvllm_tp_comm_open; within one process driving several GPUs,
+ *   nvllm_tp_comm_enable_peer + the raw pointers are enough.  comm_ptrs is a
+ *   HOST array of `world` device pointers — rank r's buffer as mapped in the
+ *   calling process, comm_ptrs[rank] being the local one.  All ranks must
+ *   issue the same sequence of calls with the same shapes (as tensor
+ *   parallelism does); calls are stream-ordered, graph-capturable, allocate
+ *   nothing and need no host synchronisation between ranks: a call epoch in
+ *   the buffer's control area advances on the device.  A peer that never
+ *   arrives makes the kernel give up after the configured timeout (default
+ *   20 s) and latch an error word readable with nvllm_tp_comm_status.
+ * ---------------------------------------------------------------------- */
+NVLLM_API size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens,
+                                    int32_t in_features_per_rank,
+                                    int32_t out_features);
+NVLLM_API int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out /* 64 bytes or NULL */);
+NVLLM_API int nvllm_tp_comm_open(const void* ipc_handle, void** peer_ptr);
+NVLLM_API int nvllm_tp_comm_close(void* peer_ptr);
+NVLLM_API int nvllm_tp_comm_free(void* dev_ptr);
+/* zero the control area (epoch, flags) again; every rank must do it between the same two calls */
+NVLLM_API int nvllm_tp_comm_reset(void* dev_ptr, void* stream);
+NVLLM_API int nvllm_tp_comm_enable_peer(int32_t peer_device);
+/* synchronous read-back of the call epoch and the latched error word (0 = none) */
+NVLLM_API int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* error_out);
+NVLLM_API int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride,
+                                       const void* x, int64_t x_row_stride,
+                                       const void* weight, int64_t w_row_stride,
+                                       const void* bias, int32_t n_tokens,
+                                       int32_t in_features_per_rank,
+                                       int32_t out_features,
+                                       void* const* comm_ptrs, size_t comm_bytes,
+                                       int32_t rank, int32_t world, void* stream);
+/* The launch plan is a function of the shape alone, so every rank agrees:
+ * feature tile (32|64 output features per CTA), k split, exchange mode
+ * (0 = one-shot: partials pushed to every rank, each rank reduces everything;
+ *  1 = two-shot: partials pushed to the tile's owner, owner broadcasts bf16). */
+NVLLM_API int nvllm_rowparallel_plan(int32_t n_tokens, int32_t in_features_per_rank,
+                           int32_t out_features, int32_t world,
+                           int32_t* feature_tile_out, int32_t* ksplit_out,
+                           int32_t* mode_out);
+/* tuning / tests: force plan fields (0, 0, -1 = automatic) and the peer timeout (<= 0 keeps it) */
+NVLLM_API int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit,
+                               int32_t mode, int64_t timeout_ms);
+
 /* Measurement aid (tools/membench.py), not on the product path: streams `bytes`
  * of `buf` with contiguous warp reads (pattern 0) or with the decode kernel's
  * 256-byte-row / token-stride access shape (pattern 1, hkv heads). */

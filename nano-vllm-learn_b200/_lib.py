@@ -38,6 +38,19 @@ SIGNATURES = {
     "nvllm_sample_tokens": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_uint64, c_uint64, c_void_p, c_size_t, c_void_p]),
     "nvllm_sample_workspace_bytes": (c_size_t, [c_int32]),
+    "nvllm_rowparallel_comm_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
+    "nvllm_tp_comm_alloc": (c_int, [c_size_t, ctypes.POINTER(c_void_p), c_void_p]),
+    "nvllm_tp_comm_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "nvllm_tp_comm_close": (c_int, [c_void_p]),
+    "nvllm_tp_comm_free": (c_int, [c_void_p]),
+    "nvllm_tp_comm_reset": (c_int, [c_void_p, c_void_p]),
+    "nvllm_tp_comm_enable_peer": (c_int, [c_int32]),
+    "nvllm_tp_comm_status": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_uint32), ctypes.POINTER(ctypes.c_uint32)]),
+    "nvllm_rowparallel_linear_allreduce": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                                   c_int32, c_int32, c_int32, ctypes.POINTER(c_void_p), c_size_t,
+                                                   c_int32, c_int32, c_void_p]),
+    "nvllm_rowparallel_plan": (c_int, [c_int32, c_int32, c_int32, c_int32, _P32, _P32, _P32]),
+    "nvllm_rowparallel_set_plan": (c_int, [c_int32, c_int32, c_int32, c_int64]),
     "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),

@@ -1,0 +1,546 @@
+// RowParallelLinear (o_proj / down_proj) GEMM + tensor-parallel all-reduce in ONE launch
+// per rank, over NVLink peer memory.  Declarations and reference citations: include/nvllm_attn.h (6).
+//
+// reference: nanovllm/layers/linear.py:185-190 — y = F.linear(x, W_r); dist.all_reduce(y)   (two launches
+// plus an NCCL kernel per call; 2 calls per decoder layer: qwen3.py:118 and qwen3.py:147).
+//
+// One CTA per (feature tile, k split, token block):
+//   1. partial[tok, f] = sum_k x[tok, k] * W[f, k] over its k range: mma.sync m16n8k16 bf16 -> fp32, operands
+//      streamed with 16-byte cp.async.cg through a 4-stage swizzled shared-memory ring (the op is bound by
+//      streaming W once from HBM and by latency: N tokens <= 512 is N flop/byte, under the tensor ridge);
+//   2. the fp32 partial tile is PUSHED with 16-byte stores into the inbox of every rank ("one-shot", mode 0) or of
+//      the tile's owner rank only ("two-shot", mode 1), then published with one st.release.sys flag per target;
+//   3. the CTA waits (ld.acquire.sys) for the world*ksplit flags of its tile, sums the partials in fixed slot order
+//      in fp32 (bit-identical on every rank), adds the bias, rounds to bf16 once and writes y (mode 0), or writes
+//      the reduced bf16 tile into every rank's result area, publishes a second flag, and every rank copies its
+//      slice into y (mode 1).
+// Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
+// epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
+// waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
+// within one co-resident wave.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace nvllm {
+namespace {
+
+constexpr int RP_THREADS = 128;
+constexpr int RP_BK = 64;          // k elements per pipeline stage: 128-byte rows
+constexpr int RP_STAGES = 4;
+constexpr int RP_TOKB = 128;       // tokens per CTA
+constexpr int RP_MAX_WORLD = 8;
+constexpr int RP_MAX_KSPLIT = 8;
+constexpr int RP_MAX_SLOTS = RP_MAX_WORLD * RP_MAX_KSPLIT;
+constexpr int RP_MAX_TILES = 1024;
+constexpr int RP_MAX_TOKENS = 512;
+constexpr int RP_PLAN_CAP = 296;    // 2 CTAs x 148 SMs
+constexpr size_t RP_HDR_BYTES = 4096;                                       // control words
+constexpr size_t RP_FLAG1_BYTES = size_t(RP_MAX_SLOTS) * RP_MAX_TILES * 4;  // [slot][tile] partial arrived
+constexpr size_t RP_FLAG2_BYTES = size_t(RP_MAX_KSPLIT) * RP_MAX_TILES * 4; // [ks][tile] reduced slice arrived
+constexpr size_t RP_DATA_OFF = RP_HDR_BYTES + RP_FLAG1_BYTES + RP_FLAG2_BYTES;
+
+struct RpControl {
+  uint32_t epoch;   // calls completed on this rank
+  uint32_t done;    // CTAs of the running call that have finished (self-resetting)
+  uint32_t error;   // 0, or 1 + the tile whose wait timed out
+};
+
+struct RpParams {
+  const __nv_bfloat16* x;
+  const __nv_bfloat16* w;
+  const __nv_bfloat16* bias;
+  __nv_bfloat16* y;
+  int64_t x_stride, w_stride, y_stride;
+  uint8_t* comm[RP_MAX_WORLD];
+  int rank, world, n_tokens, ksplit, kc, h_tiles, n_tiles, mode;
+  unsigned long long par_bytes;   // bytes of one parity's data area
+  unsigned long long res_off;     // offset of the result area inside a parity (mode 1)
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void st_v4(void* p, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_v2u(void* p, uint32_t a, uint32_t b) {
+  asm volatile("st.global.v2.u32 [%0], {%1,%2};\n" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+
+// Spin until *flag has reached `epoch` (wrap-safe); on timeout record the tile and give up.
+__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, RpControl* ctrl, int tile,
+                                          unsigned long long timeout_ns) {
+  if (static_cast<int32_t>(ld_acquire_sys(flag) - epoch) >= 0) return;
+  const unsigned long long t0 = globaltimer_ns();
+  while (static_cast<int32_t>(ld_acquire_sys(flag) - epoch) < 0) {
+    __nanosleep(32);
+    if (globaltimer_ns() - t0 > timeout_ns) {
+      atomicCAS(&ctrl->error, 0u, 1u + static_cast<uint32_t>(tile));
+      return;
+    }
+  }
+}
+
+template <int BH>
+__global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int NJ = BH / 32;             // 8-feature n-tiles per warp (4 warps split the BH features)
+  constexpr int F4 = BH / 4;              // float4 chunks per tile row
+  constexpr int EP_STRIDE = BH + 8;       // floats per staged epilogue row (padding breaks bank conflicts)
+  constexpr size_t TILE_BYTES = size_t(RP_TOKB) * BH * 4;   // inbox footprint of one (slot, tile)
+  constexpr size_t RES_TILE_BYTES = size_t(RP_TOKB) * BH * 2;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ks = blockIdx.x % p.ksplit;
+  const int tile = blockIdx.x / p.ksplit;
+  const int ht = tile % p.h_tiles;
+  const int tok0 = (tile / p.h_tiles) * RP_TOKB;
+  const int nt = min(RP_TOKB, p.n_tokens - tok0);
+  const int nt16 = (nt + 15) & ~15;
+  const int mt = nt16 >> 4;
+
+  uint8_t* const local = p.comm[p.rank];
+  RpControl* const ctrl = reinterpret_cast<RpControl*>(local);
+  __shared__ uint32_t s_epoch;
+  if (tid == 0) s_epoch = *reinterpret_cast<volatile uint32_t*>(&ctrl->epoch) + 1u;
+
+  // ---------------- 1. partial GEMM over k in [ks*kc, (ks+1)*kc) ----------------
+  const uint32_t w_stage = BH * 128, x_stage = nt16 * 128, stage_bytes = w_stage + x_stage;
+  const uint32_t sbase = smem_u32(smem);
+  const __nv_bfloat16* wsrc = p.w + static_cast<int64_t>(ht) * BH * p.w_stride + static_cast<int64_t>(ks) * p.kc;
+  const __nv_bfloat16* xsrc = p.x + static_cast<int64_t>(tok0) * p.x_stride + static_cast<int64_t>(ks) * p.kc;
+  const int nk = p.kc / RP_BK;
+
+  auto load_stage = [&](int i) {
+    const uint32_t wb = sbase + (i % RP_STAGES) * stage_bytes, xb = wb + w_stage;
+    const __nv_bfloat16* ws = wsrc + i * RP_BK;
+    const __nv_bfloat16* xs = xsrc + i * RP_BK;
+    for (int c = tid; c < BH * 8; c += RP_THREADS) {
+      const int row = c >> 3, ch = c & 7;
+      cp_async16(wb + row * 128 + ((ch ^ (row & 7)) << 4), ws + row * p.w_stride + ch * 8, 16);
+    }
+    for (int c = tid; c < nt16 * 8; c += RP_THREADS) {
+      const int row = c >> 3, ch = c & 7;
+      const bool ok = row < nt;   // rows past the last token are zero-filled
+      cp_async16(xb + row * 128 + ((ch ^ (row & 7)) << 4), xs + (ok ? row : 0) * p.x_stride + ch * 8, ok ? 16 : 0);
+    }
+  };
+
+  float acc[8][NJ][4];
+#pragma unroll
+  for (int m = 0; m < 8; ++m)
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+
+#pragma unroll
+  for (int s = 0; s < RP_STAGES - 1; ++s) {
+    if (s < nk) load_stage(s);
+    cp_async_commit();
+  }
+  for (int i = 0; i < nk; ++i) {
+    cp_async_wait<RP_STAGES - 2>();
+    __syncthreads();   // stage i landed for every thread; stage i-1 is no longer being read
+    if (i + RP_STAGES - 1 < nk) load_stage(i + RP_STAGES - 1);
+    cp_async_commit();
+    const uint32_t wb = sbase + (i % RP_STAGES) * stage_bytes, xb = wb + w_stage;
+#pragma unroll
+    for (int kk2 = 0; kk2 < 2; ++kk2) {
+      uint32_t b[NJ][4];   // {b0,b1} of k16 step 2*kk2, {b0,b1} of step 2*kk2+1
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const int row = warp * (BH / 4) + j * 8 + (lane & 7), ch = kk2 * 4 + (lane >> 3);
+        ldmatrix_x4(b[j][0], b[j][1], b[j][2], b[j][3], wb + row * 128 + ((ch ^ (row & 7)) << 4));
+      }
+#pragma unroll
+      for (int kh = 0; kh < 2; ++kh) {
+        const int kk = kk2 * 2 + kh;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          if (m < mt) {
+            uint32_t a0, a1, a2, a3;
+            const int row = m * 16 + (lane & 15), ch = kk * 2 + (lane >> 4);
+            ldmatrix_x4(a0, a1, a2, a3, xb + row * 128 + ((ch ^ (row & 7)) << 4));
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) mma_bf16_16816(acc[m][j], a0, a1, a2, a3, b[j][2 * kh], b[j][2 * kh + 1]);
+          }
+        }
+      }
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();   // the ring is free: reuse it to stage the fp32 tile [nt16][EP_STRIDE]
+
+  float* const ep = reinterpret_cast<float*>(smem);
+  {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      if (m < mt) {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+          const int col = warp * (BH / 4) + j * 8 + 2 * t;
+          *reinterpret_cast<float2*>(ep + (m * 16 + g) * EP_STRIDE + col) = make_float2(acc[m][j][0], acc[m][j][1]);
+          *reinterpret_cast<float2*>(ep + (m * 16 + g + 8) * EP_STRIDE + col) = make_float2(acc[m][j][2], acc[m][j][3]);
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---------------- 2. push the partial tile, publish it ----------------
+  const uint32_t epoch = s_epoch;
+  const size_t par_off = RP_DATA_OFF + static_cast<size_t>(epoch & 1u) * p.par_bytes;
+  const int nslots = p.world * p.ksplit;
+  const int slot = p.rank * p.ksplit + ks;
+  const int owner = tile % p.world;
+  const size_t inbox_off = par_off + (static_cast<size_t>(slot) * p.n_tiles + tile) * TILE_BYTES;
+  const int n4 = nt * F4;
+  if (p.mode == 0) {
+    for (int i = tid; i < n4; i += RP_THREADS) {
+      const float4 v = *reinterpret_cast<const float4*>(ep + (i / F4) * EP_STRIDE + (i % F4) * 4);
+      for (int d = 0; d < p.world; ++d) st_v4(p.comm[d] + inbox_off + static_cast<size_t>(i) * 16, v);
+    }
+  } else {
+    uint8_t* const dst = p.comm[owner] + inbox_off;
+    for (int i = tid; i < n4; i += RP_THREADS)
+      st_v4(dst + static_cast<size_t>(i) * 16, *reinterpret_cast<const float4*>(ep + (i / F4) * EP_STRIDE + (i % F4) * 4));
+  }
+  __threadfence_system();
+  __syncthreads();
+  {
+    const size_t flag_off = RP_HDR_BYTES + (static_cast<size_t>(slot) * RP_MAX_TILES + tile) * 4;
+    if (p.mode == 0) {
+      if (tid < p.world) st_release_sys(reinterpret_cast<uint32_t*>(p.comm[tid] + flag_off), epoch);
+    } else if (tid == 0) {
+      st_release_sys(reinterpret_cast<uint32_t*>(p.comm[owner] + flag_off), epoch);
+    }
+  }
+
+  // ---------------- 3. reduce ----------------
+  // the ksplit CTAs of a tile share its reduction: CTA ks owns token rows [r_lo, r_hi)
+  const int rows_per = (nt + p.ksplit - 1) / p.ksplit;
+  const int r_lo = min(nt, ks * rows_per), r_hi = min(nt, r_lo + rows_per);
+  const int col0 = ht * BH;
+  if (p.mode == 0 || owner == p.rank) {
+    if (tid < nslots)
+      wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + (static_cast<size_t>(tid) * RP_MAX_TILES + tile) * 4),
+                epoch, ctrl, tile, p.timeout_ns);
+    __syncthreads();
+    const uint8_t* const in0 = local + par_off + static_cast<size_t>(tile) * TILE_BYTES;
+    const size_t slot_stride = static_cast<size_t>(p.n_tiles) * TILE_BYTES;
+    for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
+      float4 s = __ldcg(reinterpret_cast<const float4*>(in0 + static_cast<size_t>(i) * 16));
+      for (int sl = 1; sl < nslots; ++sl) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(in0 + sl * slot_stride + static_cast<size_t>(i) * 16));
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      const int row = i / F4, c = (i % F4) * 4;
+      if (p.bias) {
+        const __nv_bfloat16* bp = p.bias + col0 + c;
+        s.x += __bfloat162float(bp[0]); s.y += __bfloat162float(bp[1]);
+        s.z += __bfloat162float(bp[2]); s.w += __bfloat162float(bp[3]);
+      }
+      const uint32_t lo = pack_bf16x2(s.x, s.y), hi = pack_bf16x2(s.z, s.w);
+      if (p.mode == 0) {
+        st_v2u(p.y + static_cast<int64_t>(tok0 + row) * p.y_stride + col0 + c, lo, hi);
+      } else {
+        const size_t off = par_off + p.res_off + static_cast<size_t>(tile) * RES_TILE_BYTES + static_cast<size_t>(i) * 8;
+        for (int d = 0; d < p.world; ++d) st_v2u(p.comm[d] + off, lo, hi);
+      }
+    }
+    if (p.mode != 0) {
+      __threadfence_system();
+      __syncthreads();
+      if (tid < p.world)
+        st_release_sys(reinterpret_cast<uint32_t*>(p.comm[tid] + RP_HDR_BYTES + RP_FLAG1_BYTES +
+                                                   (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4), epoch);
+    }
+  }
+  if (p.mode != 0) {
+    if (tid == 0)
+      wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + RP_FLAG1_BYTES +
+                                                  (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4),
+                epoch, ctrl, tile, p.timeout_ns);
+    __syncthreads();
+    const uint8_t* const res = local + par_off + p.res_off + static_cast<size_t>(tile) * RES_TILE_BYTES;
+    for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
+      const uint2 v = __ldcg(reinterpret_cast<const uint2*>(res + static_cast<size_t>(i) * 8));
+      st_v2u(p.y + static_cast<int64_t>(tok0 + i / F4) * p.y_stride + col0 + (i % F4) * 4, v.x, v.y);
+    }
+  }
+
+  // ---------------- call epoch: the last CTA to finish advances it ----------------
+  __syncthreads();
+  if (tid == 0) {
+    const uint32_t prev = atomicAdd(&ctrl->done, 1u);
+    if (prev == gridDim.x - 1) {
+      ctrl->done = 0;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(&ctrl->epoch) = epoch;
+    }
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+struct RpPlan {
+  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc;
+  size_t smem, par_need, res_off;
+};
+
+int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
+unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
+
+size_t rp_smem_bytes(int bh, int n_tokens) {
+  const int nt16 = n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15);
+  const size_t ring = size_t(RP_STAGES) * (size_t(bh) * 128 + size_t(nt16) * 128);
+  const size_t epi = size_t(nt16) * (bh + 8) * 4;
+  return ring > epi ? ring : epi;
+}
+
+// Co-resident CTA capacity of the current device for this instantiation and shared-memory size.  Cached per
+// (device, size) so a call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA
+// runtime call besides the launch itself.
+template <int BH>
+int rp_capacity(size_t smem, int* out) {
+  static bool attr_set[64] = {};
+  static int cache[64][RP_TOKB / 16 + 1] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  // smem is a function of nt16 alone (rp_smem_bytes): recover the bucket from the ring size
+  const size_t bucket = (smem / RP_STAGES / 128 - BH) / 16;
+  const bool cacheable = dev < 64 && bucket <= RP_TOKB / 16 && smem == size_t(RP_STAGES) * (BH + bucket * 16) * 128;
+  if (cacheable && cache[dev][bucket] > 0) {
+    *out = cache[dev][bucket];
+    return NVLLM_OK;
+  }
+  if (dev >= 64 || !attr_set[dev]) {
+    e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<BH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return record_cuda_error(e);
+    if (dev < 64) attr_set[dev] = true;
+  }
+  int occ = 0, sms = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rowparallel_allreduce_kernel<BH>, RP_THREADS, smem);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  *out = occ * sms;
+  if (cacheable) cache[dev][bucket] = occ * sms;
+  return NVLLM_OK;
+}
+
+// Shape-only plan (identical on every rank, computable without a device so nvllm_rowparallel_comm_bytes can size
+// the buffer): feature tile, k split, exchange mode; at most RP_PLAN_CAP CTAs.  The launcher checks the grid against
+// the device's real co-resident capacity.
+int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* pl) {
+  if (n_tokens <= 0 || n_tokens > RP_MAX_TOKENS || world < 2 || world > RP_MAX_WORLD) return NVLLM_ERR_UNSUPPORTED;
+  if (k_per_rank <= 0 || k_per_rank % RP_BK || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
+  const int tok_blocks = (n_tokens + RP_TOKB - 1) / RP_TOKB;
+  const int cap32 = RP_PLAN_CAP, cap64 = RP_PLAN_CAP;
+  int bh = (out_features / 32) * tok_blocks <= cap32 ? 32 : 64;
+  if (g_force_bh == 32 || g_force_bh == 64) bh = g_force_bh;
+  const int cap = bh == 32 ? cap32 : cap64;
+  const int h_tiles = out_features / bh, n_tiles = h_tiles * tok_blocks;
+  if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
+  int ksplit = 1;
+  for (int c = 2; c <= RP_MAX_KSPLIT; c *= 2) {
+    if (k_per_rank % (c * RP_BK) || k_per_rank / c < 256 || n_tiles * c > cap) break;
+    ksplit = c;
+  }
+  if (g_force_ksplit > 0) {
+    ksplit = g_force_ksplit;
+    if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
+  }
+  // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
+  const size_t pushed = size_t(world - 1) * ksplit * n_tokens * out_features * 4;
+  int mode = pushed <= (size_t(4) << 20) ? 0 : 1;
+  if (g_force_mode == 0 || g_force_mode == 1) mode = g_force_mode;
+  pl->bh = bh; pl->ksplit = ksplit; pl->mode = mode; pl->h_tiles = h_tiles; pl->tok_blocks = tok_blocks;
+  pl->n_tiles = n_tiles; pl->kc = k_per_rank / ksplit;
+  pl->smem = rp_smem_bytes(bh, n_tokens);
+  pl->res_off = size_t(world) * ksplit * n_tiles * (size_t(RP_TOKB) * bh * 4);
+  pl->par_need = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
+  return NVLLM_OK;
+}
+
+}  // namespace
+}  // namespace nvllm
+
+using namespace nvllm;
+
+extern "C" {
+
+size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens, int32_t in_features_per_rank,
+                                    int32_t out_features) {
+  // worst case of the shape-only plan over every token count and both feature tiles (a k split forced through
+  // nvllm_rowparallel_set_plan is honoured: size the buffer after forcing it)
+  if (max_tokens > RP_MAX_TOKENS) max_tokens = RP_MAX_TOKENS;
+  const int saved_bh = g_force_bh;
+  size_t need = 0;
+  for (int n = 1; n <= max_tokens; ++n)
+    for (int bh = 32; bh <= 64; bh += 32) {
+      RpPlan pl;
+      g_force_bh = bh;
+      if (rp_plan(n, in_features_per_rank, out_features, world, &pl) == NVLLM_OK && pl.par_need > need)
+        need = pl.par_need;
+    }
+  g_force_bh = saved_bh;
+  return need ? RP_DATA_OFF + 2 * need : 0;
+}
+
+int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out) {
+  if (!dev_ptr || bytes < RP_DATA_OFF) return NVLLM_ERR_BAD_ARG;
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  e = cudaMemset(p, 0, RP_DATA_OFF);   // epoch 0, flags 0; the data areas need no initial value
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e == cudaSuccess && ipc_handle_out) {
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, p);
+    if (e == cudaSuccess) memcpy(ipc_handle_out, &h, sizeof(h));
+  }
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return record_cuda_error(e);
+  }
+  *dev_ptr = p;
+  return NVLLM_OK;
+}
+
+int nvllm_tp_comm_open(const void* ipc_handle, void** peer_ptr) {
+  if (!ipc_handle || !peer_ptr) return NVLLM_ERR_BAD_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle, sizeof(h));
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  *peer_ptr = p;
+  return NVLLM_OK;
+}
+
+int nvllm_tp_comm_close(void* peer_ptr) {
+  if (!peer_ptr) return NVLLM_OK;
+  return record_cuda_error(cudaIpcCloseMemHandle(peer_ptr));
+}
+
+int nvllm_tp_comm_free(void* dev_ptr) {
+  if (!dev_ptr) return NVLLM_OK;
+  return record_cuda_error(cudaFree(dev_ptr));
+}
+
+int nvllm_tp_comm_reset(void* dev_ptr, void* stream) {
+  if (!dev_ptr) return NVLLM_ERR_BAD_ARG;
+  return record_cuda_error(cudaMemsetAsync(dev_ptr, 0, RP_DATA_OFF, static_cast<cudaStream_t>(stream)));
+}
+
+int nvllm_tp_comm_enable_peer(int32_t peer_device) {
+  int dev = 0, can = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  if (peer_device == dev) return NVLLM_OK;
+  e = cudaDeviceCanAccessPeer(&can, dev, peer_device);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  if (!can) return NVLLM_ERR_UNSUPPORTED;
+  e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    e = cudaSuccess;
+  }
+  return record_cuda_error(e);
+}
+
+int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* error_out) {
+  if (!dev_ptr) return NVLLM_ERR_BAD_ARG;
+  RpControl c;
+  cudaError_t e = cudaMemcpy(&c, dev_ptr, sizeof(c), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  if (epoch_out) *epoch_out = c.epoch;
+  if (error_out) *error_out = c.error;
+  return NVLLM_OK;
+}
+
+int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit, int32_t mode, int64_t timeout_ms) {
+  if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64)) return NVLLM_ERR_BAD_ARG;
+  if (ksplit < 0 || ksplit > RP_MAX_KSPLIT || (ksplit & (ksplit - 1))) return NVLLM_ERR_BAD_ARG;
+  if (mode < -1 || mode > 1) return NVLLM_ERR_BAD_ARG;
+  g_force_bh = feature_tile;
+  g_force_ksplit = ksplit;
+  g_force_mode = mode;
+  if (timeout_ms > 0) g_timeout_ns = static_cast<unsigned long long>(timeout_ms) * 1000000ull;
+  return NVLLM_OK;
+}
+
+int nvllm_rowparallel_plan(int32_t n_tokens, int32_t in_features_per_rank, int32_t out_features, int32_t world,
+                           int32_t* feature_tile_out, int32_t* ksplit_out, int32_t* mode_out) {
+  RpPlan pl;
+  const int st = rp_plan(n_tokens, in_features_per_rank, out_features, world, &pl);
+  if (st != NVLLM_OK) return st;
+  if (feature_tile_out) *feature_tile_out = pl.bh;
+  if (ksplit_out) *ksplit_out = pl.ksplit;
+  if (mode_out) *mode_out = pl.mode;
+  return NVLLM_OK;
+}
+
+int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void* x, int64_t x_row_stride,
+                                       const void* weight, int64_t w_row_stride, const void* bias,
+                                       int32_t n_tokens, int32_t in_features_per_rank, int32_t out_features,
+                                       void* const* comm_ptrs, size_t comm_bytes, int32_t rank, int32_t world,
+                                       void* stream) {
+  if (n_tokens == 0) return NVLLM_OK;
+  if (!y || !x || !weight || !comm_ptrs || rank < 0 || rank >= world) return NVLLM_ERR_BAD_ARG;
+  if (!aligned16(y) || !aligned16(x) || !aligned16(weight) || (y_row_stride % 8) || (x_row_stride % 8) ||
+      (w_row_stride % 8) || (bias && (reinterpret_cast<uintptr_t>(bias) & 7u)))
+    return NVLLM_ERR_ALIGNMENT;
+  if (y_row_stride < out_features || x_row_stride < in_features_per_rank || w_row_stride < in_features_per_rank)
+    return NVLLM_ERR_BAD_ARG;
+  RpPlan pl;
+  int st = rp_plan(n_tokens, in_features_per_rank, out_features, world, &pl);
+  if (st != NVLLM_OK) return st;
+  if (comm_bytes < RP_DATA_OFF + 2 * pl.par_need) return NVLLM_ERR_WORKSPACE;
+
+  int capacity = 0;   // every CTA of the grid must be co-resident (cross-rank waits inside the kernel)
+  st = pl.bh == 32 ? rp_capacity<32>(pl.smem, &capacity) : rp_capacity<64>(pl.smem, &capacity);
+  if (st != NVLLM_OK) return st;
+  if (pl.n_tiles * pl.ksplit > capacity) return NVLLM_ERR_UNSUPPORTED;
+
+  RpParams p{};
+  p.x = static_cast<const __nv_bfloat16*>(x);
+  p.w = static_cast<const __nv_bfloat16*>(weight);
+  p.bias = static_cast<const __nv_bfloat16*>(bias);
+  p.y = static_cast<__nv_bfloat16*>(y);
+  p.x_stride = x_row_stride; p.w_stride = w_row_stride; p.y_stride = y_row_stride;
+  for (int r = 0; r < world; ++r) {
+    if (!comm_ptrs[r] || !aligned16(comm_ptrs[r])) return NVLLM_ERR_BAD_ARG;
+    p.comm[r] = static_cast<uint8_t*>(comm_ptrs[r]);
+  }
+  p.rank = rank; p.world = world; p.n_tokens = n_tokens; p.ksplit = pl.ksplit; p.kc = pl.kc;
+  p.h_tiles = pl.h_tiles; p.n_tiles = pl.n_tiles; p.mode = pl.mode;
+  p.par_bytes = (comm_bytes - RP_DATA_OFF) / 2 / 16 * 16;
+  p.res_off = pl.res_off;
+  p.timeout_ns = g_timeout_ns;
+  const dim3 grid(pl.n_tiles * pl.ksplit);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (pl.bh == 32)
+    rowparallel_allreduce_kernel<32><<<grid, RP_THREADS, pl.smem, s>>>(p);
+  else
+    rowparallel_allreduce_kernel<64><<<grid, RP_THREADS, pl.smem, s>>>(p);
+  note_launch();
+  return record_cuda_error(cudaGetLastError());
+}
+
+}  // extern "C"

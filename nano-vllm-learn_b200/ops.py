@@ -264,3 +264,45 @@ def sample_tokens(logits: torch.Tensor, temperatures: torch.Tensor, noise: Optio
                                  _stream())
     _lib.check(st, "sample_tokens")
     return out
+
+
+def rowparallel_linear_allreduce(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], comm,
+                                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused RowParallelLinear.forward (nanovllm/layers/linear.py:185-190): y = all_reduce_r(x_r @ W_r^T) (+ bias),
+    GEMM and all-reduce in one launch.  x [n, in/tp] bf16 (row-strided), weight [out, in/tp] bf16, bias bf16 [out] or
+    None; `comm` is a rowparallel_cuda.TPComm (peer-mapped buffers of all ranks).  Returns a fresh [n, out] bf16."""
+    lib = _lib.load()
+    _require_cuda(x, weight, bias)
+    assert x.dim() == 2 and weight.dim() == 2 and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16
+    assert x.stride(1) == 1 and weight.stride(1) == 1
+    n, k = x.shape
+    h, k2 = weight.shape
+    assert k == k2, "x and weight shards disagree on in_features_per_rank"
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == h and bias.is_contiguous()
+    if out is None:
+        out = torch.empty((n, h), dtype=torch.bfloat16, device=x.device)
+    else:
+        assert out.shape == (n, h) and out.dtype == torch.bfloat16 and out.stride(1) == 1
+    if n == 0:
+        return out
+    st = lib.nvllm_rowparallel_linear_allreduce(out.data_ptr(), out.stride(0), x.data_ptr(), x.stride(0),
+                                                weight.data_ptr(), weight.stride(0),
+                                                bias.data_ptr() if bias is not None else None, n, k, h,
+                                                comm.ptr_array, comm.nbytes, comm.rank, comm.world, _stream())
+    _lib.check(st, "rowparallel_linear_allreduce")
+    return out
+
+
+def rowparallel_plan(n_tokens: int, in_features_per_rank: int, out_features: int, world: int) -> tuple[int, int, int]:
+    """(feature_tile, ksplit, mode) the library will use for this shape (needs a CUDA device)."""
+    import ctypes
+    lib = _lib.load()
+    bh, ks, mode = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+    _lib.check(lib.nvllm_rowparallel_plan(n_tokens, in_features_per_rank, out_features, world,
+                                          ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)), "rowparallel_plan")
+    return bh.value, ks.value, mode.value
+
+
+def rowparallel_set_plan(feature_tile: int = 0, ksplit: int = 0, mode: int = -1, timeout_ms: int = 0) -> None:
+    _lib.check(_lib.load().nvllm_rowparallel_set_plan(feature_tile, ksplit, mode, timeout_ms), "rowparallel_set_plan")

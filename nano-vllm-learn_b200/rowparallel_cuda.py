@@ -1,0 +1,173 @@
+"""Fused RowParallelLinear for tensor parallelism: GEMM + all-reduce in one sm_100a kernel over NVLink peer memory.
+
+Drop-in for `RowParallelLinear.forward` (nanovllm/layers/linear.py:185-190; o_proj at qwen3.py:118, down_proj at
+qwen3.py:147) — SURVEY §8f rank 2.  The reference launches cuBLAS, then an NCCL all-reduce on the [N, hidden]
+result (two latency-bound collectives per layer in decode); here every rank's CTAs push their fp32 partial tiles
+straight into the peers' inboxes and reduce what arrives, so one launch replaces both and no NCCL kernel runs.
+
+`TPComm` owns the peer-mapped buffers: one cudaMalloc per rank, exchanged between the rank PROCESSES (the reference
+spawns one process per GPU, llm_engine.py:29-36) as CUDA IPC handles through the existing process group.  Batches
+above `MAX_TOKENS` (long prefill: GEMM-bound, the collective is bandwidth- not latency-bound) keep the reference's
+own F.linear + dist.all_reduce.  No CPU path: CUDA tensors and the built library are required.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+from . import _lib, ops
+
+MAX_TOKENS = 512          # nvllm_rowparallel_linear_allreduce's n_tokens limit (include/nvllm_attn.h (6))
+_IPC_HANDLE_BYTES = 64
+
+
+class TPComm:
+    """Peer-mapped communication buffers of all tensor-parallel ranks, as seen from this rank's process."""
+
+    def __init__(self, rank: int, world: int, nbytes: int, local_ptr: int, peer_ptrs: list[int], how: str,
+                 keepalive=None):
+        assert len(peer_ptrs) == world and peer_ptrs[rank] == local_ptr
+        self.rank, self.world, self.nbytes, self.how = rank, world, nbytes, how
+        self.local_ptr = local_ptr
+        self.peer_ptrs = list(peer_ptrs)
+        self.ptr_array = (ctypes.c_void_p * world)(*peer_ptrs)
+        self._keepalive = keepalive
+
+    # -- construction -------------------------------------------------------------------------------------------
+    @staticmethod
+    def required_bytes(world: int, shapes: list[tuple[int, int]], max_tokens: int = MAX_TOKENS) -> int:
+        """Buffer size covering every (in_features_per_rank, out_features) in `shapes` (pure host arithmetic)."""
+        lib = _lib.load()
+        need = 0
+        for k, h in shapes:
+            b = int(lib.nvllm_rowparallel_comm_bytes(world, max_tokens, k, h))
+            if b == 0:
+                raise ValueError(f"rowparallel: unsupported shape in_features_per_rank={k} out_features={h} world={world}")
+            need = max(need, b)
+        return need
+
+    @classmethod
+    def from_process_group(cls, nbytes: int, group=None) -> "TPComm":
+        """One process per GPU (the reference's layout): cudaMalloc here, CUDA IPC handles through `group`.
+        Falls back to torch symmetric memory (also peer-mapped device memory) when legacy CUDA IPC is refused
+        by the environment; raises if neither works."""
+        import torch.distributed as dist
+        lib = _lib.load()
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        ptr = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(_IPC_HANDLE_BYTES)
+        st = lib.nvllm_tp_comm_alloc(nbytes, ctypes.byref(ptr), handle)
+        mine = (bytes(handle.raw), torch.cuda.current_device(), os.getpid()) if st == 0 else None
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine, group=group)
+        ok = all(g is not None for g in gathered)
+        ptrs = [0] * world
+        if ok:
+            for r, (h, _dev, _pid) in enumerate(gathered):
+                if r == rank:
+                    ptrs[r] = ptr.value
+                    continue
+                peer = ctypes.c_void_p()
+                if lib.nvllm_tp_comm_open(ctypes.create_string_buffer(h, _IPC_HANDLE_BYTES), ctypes.byref(peer)) != 0:
+                    ok = False
+                    break
+                ptrs[r] = peer.value
+        flags = [None] * world
+        dist.all_gather_object(flags, bool(ok), group=group)
+        if all(flags):
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+            return cls(rank, world, nbytes, ptr.value, ptrs, "cuda-ipc")
+        # some rank could not export/map: release and try torch symmetric memory on every rank
+        for r, p in enumerate(ptrs):
+            if p and r != rank:
+                lib.nvllm_tp_comm_close(ctypes.c_void_p(p))
+        if st == 0:
+            lib.nvllm_tp_comm_free(ptr)
+        return cls._from_symmetric_memory(nbytes, group)
+
+    @classmethod
+    def _from_symmetric_memory(cls, nbytes: int, group=None) -> "TPComm":
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+        hdl = symm_mem.rendezvous(buf, group)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        _lib.check(_lib.load().nvllm_tp_comm_reset(ctypes.c_void_p(ptrs[rank]), None), "tp_comm_reset")
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        return cls(rank, world, nbytes, ptrs[rank], ptrs, "symmetric-memory", keepalive=(buf, hdl))
+
+    @classmethod
+    def single_process(cls, devices: list[int], nbytes: int) -> list["TPComm"]:
+        """One process driving several GPUs (tests, microbenchmarks): direct peer access, no IPC."""
+        lib = _lib.load()
+        world = len(devices)
+        ptrs = []
+        for d in devices:
+            with torch.cuda.device(d):
+                for e in devices:
+                    _lib.check(lib.nvllm_tp_comm_enable_peer(e), f"enable peer access {d}->{e}")
+                p = ctypes.c_void_p()
+                _lib.check(lib.nvllm_tp_comm_alloc(nbytes, ctypes.byref(p), None), "tp_comm_alloc")
+                ptrs.append(p.value)
+        return [cls(r, world, nbytes, ptrs[r], ptrs, "peer-access") for r in range(world)]
+
+    # -- inspection ---------------------------------------------------------------------------------------------
+    def status(self) -> tuple[int, int]:
+        """(call epoch, latched error word) — synchronous; error != 0 means a peer never arrived."""
+        ep, err = ctypes.c_uint32(), ctypes.c_uint32()
+        _lib.check(_lib.load().nvllm_tp_comm_status(ctypes.c_void_p(self.local_ptr), ctypes.byref(ep), ctypes.byref(err)),
+                   "tp_comm_status")
+        return ep.value, err.value
+
+
+_COMM: TPComm | None = None
+_SHAPES: set[tuple[int, int]] = set()
+
+
+def enabled() -> bool:
+    return os.environ.get("NVLLM_FUSED_ALLREDUCE", "1") != "0"
+
+
+def get_comm() -> TPComm:
+    """The process-wide communicator, created on first use from the default process group and sized for every
+    RowParallelLinear registered so far (all are constructed before the first forward)."""
+    global _COMM
+    if _COMM is None:
+        import torch.distributed as dist
+        world = dist.get_world_size()
+        _COMM = TPComm.from_process_group(TPComm.required_bytes(world, sorted(_SHAPES)))
+    return _COMM
+
+
+def supported(in_features_per_rank: int, out_features: int, world: int) -> bool:
+    return 2 <= world <= 8 and in_features_per_rank % 64 == 0 and out_features % 64 == 0 and \
+        int(_lib.load().nvllm_rowparallel_comm_bytes(world, MAX_TOKENS, in_features_per_rank, out_features)) > 0
+
+
+def install(RowParallelLinear) -> None:
+    """Patch the reference class in place (INTEGRATION.md edit A7).  tp_size == 1, unsupported shapes, batches
+    above MAX_TOKENS and NVLLM_FUSED_ALLREDUCE=0 run the reference's own forward unchanged."""
+    ref_forward = RowParallelLinear.forward
+    ref_init = RowParallelLinear.__init__
+
+    def __init__(self, *args, **kwargs):
+        ref_init(self, *args, **kwargs)
+        self._nvllm_fused = bool(enabled() and self.tp_size > 1 and
+                                 supported(self.input_size_per_partition, self.output_size, self.tp_size))
+        if self._nvllm_fused:
+            _SHAPES.add((self.input_size_per_partition, self.output_size))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > MAX_TOKENS or \
+                x.dtype != torch.bfloat16 or not x.is_cuda:
+            return ref_forward(self, x)
+        return ops.rowparallel_linear_allreduce(x, self.weight, self.bias, get_comm())
+
+    RowParallelLinear.__init__ = __init__
+    RowParallelLinear.forward = forward

@@ -181,3 +181,22 @@ def make_sampler_case(name: str):
         idx = torch.randint(0, vocab, (3,), generator=g)
         logits[r, idx] = top
     return dict(logits=logits, temperatures=torch.tensor(temps, dtype=torch.float32), noise_seed=1000 + seed)
+
+
+# ---- fused RowParallelLinear -------------------------------------------------------------
+# name -> (seed, n_tokens, in_features (all ranks), out_features, world, bias)
+ROWPARALLEL_CASES = {
+    "rp_qwen06_oproj_tp2": (40, 16, 2048, 1024, 2, False),     # Qwen3-0.6B o_proj, tp=2, decode bs 16
+    "rp_qwen06_down_tp2": (41, 5, 3072, 1024, 2, False),       # down_proj, ragged token count
+    "rp_bias_tp2": (42, 33, 512, 128, 2, True),                # bias added once (rank 0 in the reference)
+    "rp_tp4": (43, 7, 1024, 256, 4, False),
+}
+
+
+def make_rowparallel_case(name: str):
+    seed, n, k, h, world, with_bias = ROWPARALLEL_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, k, generator=g).to(torch.bfloat16)
+    w = (torch.randn(h, k, generator=g) * (k ** -0.5)).to(torch.bfloat16)
+    b = torch.randn(h, generator=g).to(torch.bfloat16) if with_bias else None
+    return dict(x=x, weight=w, bias=b, world=world, n=n, k=k, h=h)
