@@ -128,10 +128,37 @@ class TPComm:
 
 _COMM: TPComm | None = None
 _SHAPES: set[tuple[int, int]] = set()
+_ENABLED = False
+# NVLLM_FUSED_ALLREDUCE: "1" fused kernel, "0" the reference's F.linear + NCCL all_reduce.
+DEFAULT_ENV = "0"
+
+
+def configure(cuda_backend: bool) -> None:
+    """Called by ModelRunner.__init__ (INTEGRATION.md edit A7) before the model is built: the fused op is part of
+    the `cuda` backend only, so the reference's other backends keep their stock collective.  Also drops the
+    communicator of a previous engine in this process (its peers are gone)."""
+    global _ENABLED
+    _ENABLED = bool(cuda_backend) and os.environ.get("NVLLM_FUSED_ALLREDUCE", DEFAULT_ENV) != "0"
+    release()
 
 
 def enabled() -> bool:
-    return os.environ.get("NVLLM_FUSED_ALLREDUCE", "1") != "0"
+    return _ENABLED
+
+
+def release() -> None:
+    global _COMM
+    _SHAPES.clear()
+    if _COMM is None:
+        return
+    comm, _COMM = _COMM, None
+    if comm.how == "cuda-ipc":
+        lib = _lib.load()
+        torch.cuda.synchronize()
+        for r, p in enumerate(comm.peer_ptrs):
+            if r != comm.rank:
+                lib.nvllm_tp_comm_close(ctypes.c_void_p(p))
+        lib.nvllm_tp_comm_free(ctypes.c_void_p(comm.local_ptr))
 
 
 def get_comm() -> TPComm:

@@ -107,10 +107,14 @@ def _patch_worker(rank, world, port, q):
         spec.loader.exec_module(mod)
         from nano_vllm_learn_b200 import rowparallel_cuda
         rowparallel_cuda.install(mod.RowParallelLinear)
+        os.environ["NVLLM_FUSED_ALLREDUCE"] = "1"
+        rowparallel_cuda.configure(False)              # another backend: every layer stays on the reference path
+        ok0 = not mod.RowParallelLinear(1024, 1024)._nvllm_fused and not rowparallel_cuda._SHAPES
+        rowparallel_cuda.configure(True)
         c = cases.make_rowparallel_case("rp_qwen06_down_tp2")
         m = mod.RowParallelLinear(c["k"], c["h"]).to(torch.bfloat16)
         m.weight.weight_loader(m.weight, c["weight"])
-        ok = m._nvllm_fused and (c["k"] // world, c["h"]) in rowparallel_cuda._SHAPES
+        ok = ok0 and m._nvllm_fused and (c["k"] // world, c["h"]) in rowparallel_cuda._SHAPES
         odd = mod.RowParallelLinear(200, 100)          # shape the kernel does not take: stays on the reference path
         ok = ok and not odd._nvllm_fused
         # CPU tensors never reach the CUDA op: the patched forward must be the reference's own

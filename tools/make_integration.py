@@ -3,7 +3,7 @@
     python tools/make_integration.py [--src baseline/_ref] [--dst build/nanovllm_cuda]
 
 Copies `<src>/nanovllm` to `<dst>/nanovllm` (git-ignored, never committed) and applies exactly the
-edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5/A6), plus two environment-compat
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5/A6/A7), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
 anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
@@ -49,6 +49,18 @@ EDITS = [
      '        if attn_backend == "cuda" and __import__("os").environ.get("NVLLM_FUSED_SAMPLER", "1") != "0":\n'
      '            from nano_vllm_learn_b200.sampler_cuda import Sampler as _CudaSampler\n'
      '            self.sampler = _CudaSampler()\n'),
+    # ---- A7 (optional: NVLLM_FUSED_ALLREDUCE=0 keeps F.linear + NCCL all_reduce):
+    #      RowParallelLinear GEMM + all-reduce in one launch over NVLink peer memory when tensor_parallel_size > 1
+    #      (nanovllm/layers/linear.py:185-190; o_proj qwen3.py:118, down_proj qwen3.py:147), appended to linear.py
+    ("nanovllm/layers/linear.py", None,
+     '\n\n# --- cuda backend: fused RowParallelLinear (GEMM + tensor-parallel all-reduce, one sm_100a kernel)\n'
+     'from nano_vllm_learn_b200.rowparallel_cuda import install as _install_fused_rowparallel\n'
+     '_install_fused_rowparallel(RowParallelLinear)\n'),
+    ("nanovllm/engine/model_runner.py",
+     '        self.model = Qwen3ForCausalLM(hf_config)\n',
+     '        from nano_vllm_learn_b200 import rowparallel_cuda as _fused_rowparallel   # A7: only with the cuda backend\n'
+     '        _fused_rowparallel.configure(attn_backend == "cuda")\n'
+     '        self.model = Qwen3ForCausalLM(hf_config)\n'),
     # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
     ("nanovllm/config.py",
      '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',
