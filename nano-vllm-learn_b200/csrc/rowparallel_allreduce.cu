@@ -343,6 +343,18 @@ int rp_capacity(size_t smem, int* out) {
   return NVLLM_OK;
 }
 
+// Load both instantiations on the current device and opt them into large dynamic shared memory, so that the first
+// launch on a device never triggers lazy module loading (which may synchronise the context) while a peer's kernel is
+// already spinning on this rank's flags.  Called from nvllm_tp_comm_alloc / nvllm_tp_comm_reset.
+cudaError_t rp_warm_device() {
+  cudaFuncAttributes fa;
+  cudaError_t e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rowparallel_allreduce_kernel<32>);
+  if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rowparallel_allreduce_kernel<64>);
+  return e;
+}
+
 // Shape-only plan (identical on every rank, computable without a device so nvllm_rowparallel_comm_bytes can size
 // the buffer): feature tile, k split, exchange mode; at most RP_PLAN_CAP CTAs.  The launcher checks the grid against
 // the device's real co-resident capacity.
@@ -405,7 +417,9 @@ size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens, int32_t i
 int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out) {
   if (!dev_ptr || bytes < RP_DATA_OFF) return NVLLM_ERR_BAD_ARG;
   void* p = nullptr;
-  cudaError_t e = cudaMalloc(&p, bytes);
+  cudaError_t e = rp_warm_device();
+  if (e != cudaSuccess) return record_cuda_error(e);
+  e = cudaMalloc(&p, bytes);
   if (e != cudaSuccess) return record_cuda_error(e);
   e = cudaMemset(p, 0, RP_DATA_OFF);   // epoch 0, flags 0; the data areas need no initial value
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -445,6 +459,8 @@ int nvllm_tp_comm_free(void* dev_ptr) {
 
 int nvllm_tp_comm_reset(void* dev_ptr, void* stream) {
   if (!dev_ptr) return NVLLM_ERR_BAD_ARG;
+  const cudaError_t e = rp_warm_device();
+  if (e != cudaSuccess) return record_cuda_error(e);
   return record_cuda_error(cudaMemsetAsync(dev_ptr, 0, RP_DATA_OFF, static_cast<cudaStream_t>(stream)));
 }
 

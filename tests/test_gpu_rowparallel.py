@@ -48,11 +48,13 @@ def comms(lib):
 def _run_world(comms, xs, ws, bias, outs=None):
     """Launch rank 0 and rank 1 back to back WITHOUT synchronising in between (the kernels wait for each other)."""
     from nano_vllm_learn_b200 import ops
+    if outs is None:   # allocate before the first launch: no cudaMalloc while a peer's kernel is spinning
+        outs = [torch.empty((xs[r].shape[0], ws[r].shape[0]), dtype=torch.bfloat16, device=f"cuda:{r}")
+                for r in range(len(comms))]
     ys = []
     for r, comm in enumerate(comms):
         with torch.cuda.device(r):
-            ys.append(ops.rowparallel_linear_allreduce(xs[r], ws[r], bias[r] if bias else None, comm,
-                                                       out=outs[r] if outs else None))
+            ys.append(ops.rowparallel_linear_allreduce(xs[r], ws[r], bias[r] if bias else None, comm, out=outs[r]))
     for r in range(len(comms)):
         torch.cuda.synchronize(r)
     return ys
