@@ -4,20 +4,26 @@
 // reference: nanovllm/layers/linear.py:185-190 — y = F.linear(x, W_r); dist.all_reduce(y)   (two launches
 // plus an NCCL kernel per call; 2 calls per decoder layer: qwen3.py:118 and qwen3.py:147).
 //
-// One CTA per (feature tile, k split, token block):
+// One CTA per (feature tile, k split, token block); the ksplit CTAs of a tile form one thread-block CLUSTER:
 //   1. partial[tok, f] = sum_k x[tok, k] * W[f, k] over its k range: mma.sync m16n8k16 bf16 -> fp32, operands
-//      streamed with 16-byte cp.async.cg through a 4-stage swizzled shared-memory ring (the op is bound by
-//      streaming W once from HBM and by latency: N tokens <= 512 is N flop/byte, under the tensor ridge);
-//   2. the fp32 partial tile is PUSHED with 16-byte stores into the inbox of every rank ("one-shot", mode 0) or of
-//      the tile's owner rank only ("two-shot", mode 1), then published with one st.release.sys flag per target;
-//   3. the CTA waits (ld.acquire.sys) for the world*ksplit flags of its tile, sums the partials in fixed slot order
-//      in fp32 (bit-identical on every rank), adds the bias, rounds to bf16 once and writes y (mode 0), or writes
-//      the reduced bf16 tile into every rank's result area, publishes a second flag, and every rank copies its
-//      slice into y (mode 1).
+//      streamed with 16-byte cp.async.cg through a 4/6/8-stage swizzled shared-memory ring, as deep as two CTAs per
+//      SM allow (the op is bound by streaming W once from HBM and by latency: N tokens <= 512 is N flop/byte,
+//      under the tensor ridge; ~100 KB in flight per SM hides the HBM latency);
+//   2. the k splits are summed INSIDE the cluster through distributed shared memory (CTA ks owns a slice of the
+//      tile's token rows and reads that slice from every CTA of the cluster, fixed order), so one fp32 partial per
+//      rank and tile crosses NVLink, not ksplit of them; the slice is PUSHED with 16-byte stores into the inbox of
+//      every rank ("one-shot", mode 0) or of the tile's owner rank only ("two-shot", mode 1), then published with
+//      one st.release.sys flag per target;
+//   3. the CTA waits (ld.acquire.sys) for the `world` flags of its row slice, sums the ranks' partials in rank
+//      order in fp32 (bit-identical on every rank), adds the bias, rounds to bf16 once and writes y (mode 0), or
+//      writes the reduced bf16 slice into every rank's result area, publishes a second flag, and every rank copies
+//      its slice into y (mode 1).
 // Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
 // epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
 // waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
 // within one co-resident wave.
+#include <cooperative_groups.h>
+
 #include <cstring>
 
 #include "common.cuh"
@@ -27,7 +33,6 @@ namespace {
 
 constexpr int RP_THREADS = 128;
 constexpr int RP_BK = 64;          // k elements per pipeline stage: 128-byte rows
-constexpr int RP_STAGES = 4;
 constexpr int RP_TOKB = 128;       // tokens per CTA
 constexpr int RP_MAX_WORLD = 8;
 constexpr int RP_MAX_KSPLIT = 8;
@@ -93,7 +98,10 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
   }
 }
 
-template <int BH>
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;\n" ::: "memory"); }
+
+template <int BH, int STAGES>
 __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int NJ = BH / 32;             // 8-feature n-tiles per warp (4 warps split the BH features)
@@ -124,7 +132,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   const int nk = p.kc / RP_BK;
 
   auto load_stage = [&](int i) {
-    const uint32_t wb = sbase + (i % RP_STAGES) * stage_bytes, xb = wb + w_stage;
+    const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
     const __nv_bfloat16* ws = wsrc + i * RP_BK;
     const __nv_bfloat16* xs = xsrc + i * RP_BK;
     for (int c = tid; c < BH * 8; c += RP_THREADS) {
@@ -147,16 +155,16 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
 
 #pragma unroll
-  for (int s = 0; s < RP_STAGES - 1; ++s) {
+  for (int s = 0; s < STAGES - 1; ++s) {
     if (s < nk) load_stage(s);
     cp_async_commit();
   }
   for (int i = 0; i < nk; ++i) {
-    cp_async_wait<RP_STAGES - 2>();
+    cp_async_wait<STAGES - 2>();
     __syncthreads();   // stage i landed for every thread; stage i-1 is no longer being read
-    if (i + RP_STAGES - 1 < nk) load_stage(i + RP_STAGES - 1);
+    if (i + STAGES - 1 < nk) load_stage(i + STAGES - 1);
     cp_async_commit();
-    const uint32_t wb = sbase + (i % RP_STAGES) * stage_bytes, xb = wb + w_stage;
+    const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
 #pragma unroll
     for (int kk2 = 0; kk2 < 2; ++kk2) {
       uint32_t b[NJ][4];   // {b0,b1} of k16 step 2*kk2, {b0,b1} of step 2*kk2+1
@@ -199,30 +207,48 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       }
     }
   }
-  __syncthreads();
+  // every CTA of the cluster has staged its k-split partial (release/acquire at cluster scope covers the
+  // distributed-shared-memory reads below)
+  cluster_arrive();
+  cluster_wait();
 
-  // ---------------- 2. push the partial tile, publish it ----------------
+  // ---------------- 2. sum the k splits of this CTA's row slice, push it, publish it ----------------
+  // the ksplit CTAs of a tile share its reduction: CTA ks owns token rows [r_lo, r_hi)
   const uint32_t epoch = s_epoch;
   const size_t par_off = RP_DATA_OFF + static_cast<size_t>(epoch & 1u) * p.par_bytes;
-  const int nslots = p.world * p.ksplit;
-  const int slot = p.rank * p.ksplit + ks;
   const int owner = tile % p.world;
-  const size_t inbox_off = par_off + (static_cast<size_t>(slot) * p.n_tiles + tile) * TILE_BYTES;
-  const int n4 = nt * F4;
-  if (p.mode == 0) {
-    for (int i = tid; i < n4; i += RP_THREADS) {
-      const float4 v = *reinterpret_cast<const float4*>(ep + (i / F4) * EP_STRIDE + (i % F4) * 4);
-      for (int d = 0; d < p.world; ++d) st_v4(p.comm[d] + inbox_off + static_cast<size_t>(i) * 16, v);
-    }
-  } else {
-    uint8_t* const dst = p.comm[owner] + inbox_off;
-    for (int i = tid; i < n4; i += RP_THREADS)
-      st_v4(dst + static_cast<size_t>(i) * 16, *reinterpret_cast<const float4*>(ep + (i / F4) * EP_STRIDE + (i % F4) * 4));
-  }
-  __threadfence_system();
-  __syncthreads();
+  const int rows_per = (nt + p.ksplit - 1) / p.ksplit;
+  const int r_lo = min(nt, ks * rows_per), r_hi = min(nt, r_lo + rows_per);
+  const bool has_rows = r_hi > r_lo;   // CTA-uniform, and the same on every rank
+  const size_t inbox_off = par_off + (static_cast<size_t>(p.rank) * p.n_tiles + tile) * TILE_BYTES;
   {
-    const size_t flag_off = RP_HDR_BYTES + (static_cast<size_t>(slot) * RP_MAX_TILES + tile) * 4;
+    const float* epc[RP_MAX_KSPLIT];
+    cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+#pragma unroll
+    for (int c = 0; c < RP_MAX_KSPLIT; ++c) epc[c] = c < p.ksplit ? cluster.map_shared_rank(ep, c) : ep;
+    uint8_t* const dst1 = p.comm[owner] + inbox_off;
+    for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
+      const int off = (i / F4) * EP_STRIDE + (i % F4) * 4;
+      float4 s = *reinterpret_cast<const float4*>(epc[0] + off);
+#pragma unroll
+      for (int c = 1; c < RP_MAX_KSPLIT; ++c) {
+        if (c < p.ksplit) {
+          const float4 v = *reinterpret_cast<const float4*>(epc[c] + off);
+          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+      }
+      if (p.mode == 0) {
+        for (int d = 0; d < p.world; ++d) st_v4(p.comm[d] + inbox_off + static_cast<size_t>(i) * 16, s);
+      } else {
+        st_v4(dst1 + static_cast<size_t>(i) * 16, s);
+      }
+    }
+  }
+  cluster_arrive();   // this CTA no longer reads its peers' shared memory (waited for before exit)
+  const size_t flag_off = RP_HDR_BYTES + (static_cast<size_t>(p.rank * p.ksplit + ks) * RP_MAX_TILES + tile) * 4;
+  if (has_rows) {
+    // the release below is cumulative over the CTA barrier: it orders every thread's pushed stores before the flag
+    __syncthreads();
     if (p.mode == 0) {
       if (tid < p.world) st_release_sys(reinterpret_cast<uint32_t*>(p.comm[tid] + flag_off), epoch);
     } else if (tid == 0) {
@@ -230,21 +256,19 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     }
   }
 
-  // ---------------- 3. reduce ----------------
-  // the ksplit CTAs of a tile share its reduction: CTA ks owns token rows [r_lo, r_hi)
-  const int rows_per = (nt + p.ksplit - 1) / p.ksplit;
-  const int r_lo = min(nt, ks * rows_per), r_hi = min(nt, r_lo + rows_per);
+  // ---------------- 3. reduce over ranks ----------------
   const int col0 = ht * BH;
-  if (p.mode == 0 || owner == p.rank) {
-    if (tid < nslots)
-      wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + (static_cast<size_t>(tid) * RP_MAX_TILES + tile) * 4),
+  if (has_rows && (p.mode == 0 || owner == p.rank)) {
+    if (tid < p.world)
+      wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES +
+                                                  (static_cast<size_t>(tid * p.ksplit + ks) * RP_MAX_TILES + tile) * 4),
                 epoch, ctrl, tile, p.timeout_ns);
     __syncthreads();
     const uint8_t* const in0 = local + par_off + static_cast<size_t>(tile) * TILE_BYTES;
     const size_t slot_stride = static_cast<size_t>(p.n_tiles) * TILE_BYTES;
     for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
       float4 s = __ldcg(reinterpret_cast<const float4*>(in0 + static_cast<size_t>(i) * 16));
-      for (int sl = 1; sl < nslots; ++sl) {
+      for (int sl = 1; sl < p.world; ++sl) {
         const float4 v = __ldcg(reinterpret_cast<const float4*>(in0 + sl * slot_stride + static_cast<size_t>(i) * 16));
         s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
@@ -263,14 +287,13 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       }
     }
     if (p.mode != 0) {
-      __threadfence_system();
       __syncthreads();
       if (tid < p.world)
         st_release_sys(reinterpret_cast<uint32_t*>(p.comm[tid] + RP_HDR_BYTES + RP_FLAG1_BYTES +
                                                    (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4), epoch);
     }
   }
-  if (p.mode != 0) {
+  if (has_rows && p.mode != 0) {
     if (tid == 0)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + RP_FLAG1_BYTES +
                                                   (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4),
@@ -282,6 +305,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       st_v2u(p.y + static_cast<int64_t>(tok0 + i / F4) * p.y_stride + col0 + (i % F4) * 4, v.x, v.y);
     }
   }
+  cluster_wait();   // every CTA of the cluster is done with this CTA's shared memory
 
   // ---------------- call epoch: the last CTA to finish advances it ----------------
   __syncthreads();
@@ -297,75 +321,114 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 
 // ---- host side ---------------------------------------------------------------------------------------------
 struct RpPlan {
-  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc;
+  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, stages;
   size_t smem, par_need, res_off;
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
 unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
 
+int rp_nt16(int n_tokens) { return n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15); }
+
+// Ring depth: as deep as lets two CTAs share an SM's shared memory (8 stages of a 16-token decode tile keep
+// 2 x 7 x 6 KB = 84 KB of loads in flight per SM).
+int rp_stages(int bh, int nt16) {
+  const size_t stage = size_t(bh + nt16) * 128, budget = size_t(100) * 1024;
+  return 8 * stage <= budget ? 8 : 6 * stage <= budget ? 6 : 4;
+}
+
 size_t rp_smem_bytes(int bh, int n_tokens) {
-  const int nt16 = n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15);
-  const size_t ring = size_t(RP_STAGES) * (size_t(bh) * 128 + size_t(nt16) * 128);
+  const int nt16 = rp_nt16(n_tokens);
+  const size_t ring = size_t(rp_stages(bh, nt16)) * (size_t(bh) + nt16) * 128;
   const size_t epi = size_t(nt16) * (bh + 8) * 4;
   return ring > epi ? ring : epi;
 }
 
-// Co-resident CTA capacity of the current device for this instantiation and shared-memory size.  Cached per
-// (device, size) so a call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA
-// runtime call besides the launch itself.
-template <int BH>
-int rp_capacity(size_t smem, int* out) {
-  static bool attr_set[64] = {};
-  static int cache[64][RP_TOKB / 16 + 1] = {};
+const void* rp_kernel(int bh, int stages) {
+  if (bh == 32)
+    return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 8>)
+           : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 6>)
+                         : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 4>);
+  return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 8>)
+         : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 6>)
+                       : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 4>);
+}
+
+// Load every instantiation on the current device and opt it into large dynamic shared memory, so that the first
+// launch on a device never triggers lazy module loading (which may synchronise the context) while a peer's kernel is
+// already spinning on this rank's flags.  Called from nvllm_tp_comm_alloc / nvllm_tp_comm_reset and, once per device,
+// from the launcher.
+cudaError_t rp_warm_device() {
+  static bool done[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && done[dev]) return cudaSuccess;
+  for (int bh = 32; bh <= 64; bh += 32)
+    for (int st = 4; st <= 8; st += 2) {
+      cudaFuncAttributes fa;
+      e = cudaFuncSetAttribute(rp_kernel(bh, st), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+      if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, st));
+      if (e != cudaSuccess) return e;
+    }
+  if (dev < 64) done[dev] = true;
+  return cudaSuccess;
+}
+
+void rp_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int n_ctas, int ksplit, size_t smem,
+                      cudaStream_t s) {
+  *cfg = cudaLaunchConfig_t{};
+  cfg->gridDim = dim3(n_ctas);
+  cfg->blockDim = dim3(RP_THREADS);
+  cfg->dynamicSmemBytes = smem;
+  cfg->stream = s;
+  attr->id = cudaLaunchAttributeClusterDimension;
+  attr->val.clusterDim.x = ksplit;
+  attr->val.clusterDim.y = 1;
+  attr->val.clusterDim.z = 1;
+  cfg->attrs = attr;
+  cfg->numAttrs = 1;
+}
+
+// Co-resident cluster capacity of the current device for (feature tile, token bucket, cluster size).  Cached, so a
+// call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA runtime call besides the
+// launch itself.
+int rp_max_clusters(int bh, int nt16, int stages, size_t smem, int ksplit, int* out) {
+  static int cache[64][2][RP_TOKB / 16 + 1][4] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return record_cuda_error(e);
-  // smem is a function of nt16 alone (rp_smem_bytes): recover the bucket from the ring size
-  const size_t bucket = (smem / RP_STAGES / 128 - BH) / 16;
-  const bool cacheable = dev < 64 && bucket <= RP_TOKB / 16 && smem == size_t(RP_STAGES) * (BH + bucket * 16) * 128;
-  if (cacheable && cache[dev][bucket] > 0) {
-    *out = cache[dev][bucket];
+  const int lg = ksplit == 1 ? 0 : ksplit == 2 ? 1 : ksplit == 4 ? 2 : 3;
+  int* slot = dev < 64 ? &cache[dev][bh == 64][nt16 / 16][lg] : nullptr;
+  if (slot && *slot > 0) {
+    *out = *slot;
     return NVLLM_OK;
   }
-  if (dev >= 64 || !attr_set[dev]) {
-    e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<BH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return record_cuda_error(e);
-    if (dev < 64) attr_set[dev] = true;
-  }
-  int occ = 0, sms = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rowparallel_allreduce_kernel<BH>, RP_THREADS, smem);
+  e = rp_warm_device();
   if (e != cudaSuccess) return record_cuda_error(e);
-  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr;
+  rp_launch_config(&cfg, &attr, RP_PLAN_CAP / ksplit * ksplit, ksplit, smem, nullptr);
+  int n = 0;
+  e = cudaOccupancyMaxActiveClusters(&n, rp_kernel(bh, stages), &cfg);
   if (e != cudaSuccess) return record_cuda_error(e);
-  *out = occ * sms;
-  if (cacheable) cache[dev][bucket] = occ * sms;
+  *out = n;
+  if (slot) *slot = n;
   return NVLLM_OK;
 }
 
-// Load both instantiations on the current device and opt them into large dynamic shared memory, so that the first
-// launch on a device never triggers lazy module loading (which may synchronise the context) while a peer's kernel is
-// already spinning on this rank's flags.  Called from nvllm_tp_comm_alloc / nvllm_tp_comm_reset.
-cudaError_t rp_warm_device() {
-  cudaFuncAttributes fa;
-  cudaError_t e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(rowparallel_allreduce_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rowparallel_allreduce_kernel<32>);
-  if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rowparallel_allreduce_kernel<64>);
-  return e;
-}
-
 // Shape-only plan (identical on every rank, computable without a device so nvllm_rowparallel_comm_bytes can size
-// the buffer): feature tile, k split, exchange mode; at most RP_PLAN_CAP CTAs.  The launcher checks the grid against
-// the device's real co-resident capacity.
+// the buffer): feature tile, k split (= cluster size), exchange mode; at most RP_PLAN_CAP CTAs.  The launcher halves
+// the k split while the grid exceeds the device's real co-resident cluster capacity (the same on every rank of a
+// homogeneous node; the inbox layout does not depend on the k split).
 int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* pl) {
   if (n_tokens <= 0 || n_tokens > RP_MAX_TOKENS || world < 2 || world > RP_MAX_WORLD) return NVLLM_ERR_UNSUPPORTED;
   if (k_per_rank <= 0 || k_per_rank % RP_BK || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
   const int tok_blocks = (n_tokens + RP_TOKB - 1) / RP_TOKB;
-  const int cap32 = RP_PLAN_CAP, cap64 = RP_PLAN_CAP;
-  int bh = (out_features / 32) * tok_blocks <= cap32 ? 32 : 64;
+  const int cap = RP_PLAN_CAP;
+  // 64-feature tiles once the x tile (re-read by every feature tile) outweighs the W tile
+  int bh = (n_tokens <= 64 && (out_features / 32) * tok_blocks <= cap) ? 32 : 64;
   if (g_force_bh == 32 || g_force_bh == 64) bh = g_force_bh;
-  const int cap = bh == 32 ? cap32 : cap64;
   const int h_tiles = out_features / bh, n_tiles = h_tiles * tok_blocks;
   if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
   int ksplit = 1;
@@ -378,13 +441,14 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
     if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
   }
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
-  const size_t pushed = size_t(world - 1) * ksplit * n_tokens * out_features * 4;
+  const size_t pushed = size_t(world - 1) * n_tokens * out_features * 4;
   int mode = pushed <= (size_t(4) << 20) ? 0 : 1;
   if (g_force_mode == 0 || g_force_mode == 1) mode = g_force_mode;
   pl->bh = bh; pl->ksplit = ksplit; pl->mode = mode; pl->h_tiles = h_tiles; pl->tok_blocks = tok_blocks;
   pl->n_tiles = n_tiles; pl->kc = k_per_rank / ksplit;
+  pl->stages = rp_stages(bh, rp_nt16(n_tokens));
   pl->smem = rp_smem_bytes(bh, n_tokens);
-  pl->res_off = size_t(world) * ksplit * n_tiles * (size_t(RP_TOKB) * bh * 4);
+  pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);   // one inbox slot per rank
   pl->par_need = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
   return NVLLM_OK;
 }
@@ -529,10 +593,18 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   if (st != NVLLM_OK) return st;
   if (comm_bytes < RP_DATA_OFF + 2 * pl.par_need) return NVLLM_ERR_WORKSPACE;
 
-  int capacity = 0;   // every CTA of the grid must be co-resident (cross-rank waits inside the kernel)
-  st = pl.bh == 32 ? rp_capacity<32>(pl.smem, &capacity) : rp_capacity<64>(pl.smem, &capacity);
-  if (st != NVLLM_OK) return st;
-  if (pl.n_tiles * pl.ksplit > capacity) return NVLLM_ERR_UNSUPPORTED;
+  // every CTA of the grid must be co-resident (cross-rank waits inside the kernel): shrink the cluster while the
+  // device cannot hold all of them at once
+  const int nt16 = rp_nt16(n_tokens);
+  for (;;) {
+    int max_clusters = 0;
+    st = rp_max_clusters(pl.bh, nt16, pl.stages, pl.smem, pl.ksplit, &max_clusters);
+    if (st != NVLLM_OK) return st;
+    if (pl.n_tiles <= max_clusters) break;
+    if (pl.ksplit == 1 || g_force_ksplit > 0) return NVLLM_ERR_UNSUPPORTED;
+    pl.ksplit /= 2;
+    pl.kc *= 2;
+  }
 
   RpParams p{};
   p.x = static_cast<const __nv_bfloat16*>(x);
@@ -549,12 +621,12 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   p.par_bytes = (comm_bytes - RP_DATA_OFF) / 2 / 16 * 16;
   p.res_off = pl.res_off;
   p.timeout_ns = g_timeout_ns;
-  const dim3 grid(pl.n_tiles * pl.ksplit);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (pl.bh == 32)
-    rowparallel_allreduce_kernel<32><<<grid, RP_THREADS, pl.smem, s>>>(p);
-  else
-    rowparallel_allreduce_kernel<64><<<grid, RP_THREADS, pl.smem, s>>>(p);
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr;
+  rp_launch_config(&cfg, &attr, pl.n_tiles * pl.ksplit, pl.ksplit, pl.smem, static_cast<cudaStream_t>(stream));
+  void* args[] = {&p};
+  const cudaError_t le = cudaLaunchKernelExC(&cfg, rp_kernel(pl.bh, pl.stages), args);
+  if (le != cudaSuccess) return record_cuda_error(le);
   note_launch();
   return record_cuda_error(cudaGetLastError());
 }

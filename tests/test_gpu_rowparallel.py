@@ -172,8 +172,12 @@ def test_cuda_graph_replay(comms):
     graphs = []
     for r in range(2):
         with torch.cuda.device(r):
+            # torch.cuda.graph's default capture stream is ONE process-wide stream on whichever device captured first;
+            # entering it switches the current device, so rank 1's kernels would be recorded on cuda:0.  One capture
+            # stream per device (the engine has one process per GPU and never sees this).
             gr = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gr):
+            with torch.cuda.graph(gr, stream=torch.cuda.Stream(device=r)):
+                assert torch.cuda.current_device() == r
                 for j in range(6):
                     ops.rowparallel_linear_allreduce(xd[r], wd[r], None, comms[r], out=outs[r][j])
             graphs.append(gr)
