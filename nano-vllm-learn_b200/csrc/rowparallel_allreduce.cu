@@ -24,6 +24,7 @@
 // within one co-resident wave.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -32,7 +33,7 @@ namespace nvllm {
 namespace {
 
 constexpr int RP_THREADS = 128;
-constexpr int RP_BK = 64;          // k elements per pipeline stage: 128-byte rows
+constexpr int RP_BK_MIN = 64;      // k elements per pipeline stage: 64 (128-byte rows) or 128 (256-byte rows)
 constexpr int RP_TOKB = 128;       // tokens per CTA
 constexpr int RP_MAX_WORLD = 8;
 constexpr int RP_MAX_KSPLIT = 8;
@@ -101,7 +102,7 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;\n" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;\n" ::: "memory"); }
 
-template <int BH, int STAGES>
+template <int BH, int STAGES, int BK>
 __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int NJ = BH / 32;             // 8-feature n-tiles per warp (4 warps split the BH features)
@@ -125,24 +126,26 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   if (tid == 0) s_epoch = *reinterpret_cast<volatile uint32_t*>(&ctrl->epoch) + 1u;
 
   // ---------------- 1. partial GEMM over k in [ks*kc, (ks+1)*kc) ----------------
-  const uint32_t w_stage = BH * 128, x_stage = nt16 * 128, stage_bytes = w_stage + x_stage;
+  constexpr int ROWB = BK * 2;            // bytes per staged row
+  constexpr int CPR = BK / 8;             // 16-byte chunks per staged row; chunks are XOR-swizzled by (row & 7)
+  const uint32_t w_stage = BH * ROWB, x_stage = nt16 * ROWB, stage_bytes = w_stage + x_stage;
   const uint32_t sbase = smem_u32(smem);
   const __nv_bfloat16* wsrc = p.w + static_cast<int64_t>(ht) * BH * p.w_stride + static_cast<int64_t>(ks) * p.kc;
   const __nv_bfloat16* xsrc = p.x + static_cast<int64_t>(tok0) * p.x_stride + static_cast<int64_t>(ks) * p.kc;
-  const int nk = p.kc / RP_BK;
+  const int nk = p.kc / BK;
 
   auto load_stage = [&](int i) {
     const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
-    const __nv_bfloat16* ws = wsrc + i * RP_BK;
-    const __nv_bfloat16* xs = xsrc + i * RP_BK;
-    for (int c = tid; c < BH * 8; c += RP_THREADS) {
-      const int row = c >> 3, ch = c & 7;
-      cp_async16(wb + row * 128 + ((ch ^ (row & 7)) << 4), ws + row * p.w_stride + ch * 8, 16);
+    const __nv_bfloat16* ws = wsrc + i * BK;
+    const __nv_bfloat16* xs = xsrc + i * BK;
+    for (int c = tid; c < BH * CPR; c += RP_THREADS) {
+      const int row = c / CPR, ch = c % CPR;
+      cp_async16(wb + row * ROWB + ((ch ^ (row & 7)) << 4), ws + row * p.w_stride + ch * 8, 16);
     }
-    for (int c = tid; c < nt16 * 8; c += RP_THREADS) {
-      const int row = c >> 3, ch = c & 7;
+    for (int c = tid; c < nt16 * CPR; c += RP_THREADS) {
+      const int row = c / CPR, ch = c % CPR;
       const bool ok = row < nt;   // rows past the last token are zero-filled
-      cp_async16(xb + row * 128 + ((ch ^ (row & 7)) << 4), xs + (ok ? row : 0) * p.x_stride + ch * 8, ok ? 16 : 0);
+      cp_async16(xb + row * ROWB + ((ch ^ (row & 7)) << 4), xs + (ok ? row : 0) * p.x_stride + ch * 8, ok ? 16 : 0);
     }
   };
 
@@ -166,12 +169,12 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     cp_async_commit();
     const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
 #pragma unroll
-    for (int kk2 = 0; kk2 < 2; ++kk2) {
+    for (int kk2 = 0; kk2 < BK / 32; ++kk2) {
       uint32_t b[NJ][4];   // {b0,b1} of k16 step 2*kk2, {b0,b1} of step 2*kk2+1
 #pragma unroll
       for (int j = 0; j < NJ; ++j) {
         const int row = warp * (BH / 4) + j * 8 + (lane & 7), ch = kk2 * 4 + (lane >> 3);
-        ldmatrix_x4(b[j][0], b[j][1], b[j][2], b[j][3], wb + row * 128 + ((ch ^ (row & 7)) << 4));
+        ldmatrix_x4(b[j][0], b[j][1], b[j][2], b[j][3], wb + row * ROWB + ((ch ^ (row & 7)) << 4));
       }
 #pragma unroll
       for (int kh = 0; kh < 2; ++kh) {
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
           if (m < mt) {
             uint32_t a0, a1, a2, a3;
             const int row = m * 16 + (lane & 15), ch = kk * 2 + (lane >> 4);
-            ldmatrix_x4(a0, a1, a2, a3, xb + row * 128 + ((ch ^ (row & 7)) << 4));
+            ldmatrix_x4(a0, a1, a2, a3, xb + row * ROWB + ((ch ^ (row & 7)) << 4));
 #pragma unroll
             for (int j = 0; j < NJ; ++j) mma_bf16_16816(acc[m][j], a0, a1, a2, a3, b[j][2 * kh], b[j][2 * kh + 1]);
           }
@@ -239,14 +242,23 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       }
       if (p.mode == 0) {
         for (int d = 0; d < p.world; ++d) st_v4(p.comm[d] + inbox_off + static_cast<size_t>(i) * 16, s);
-      } else {
+      } else if (p.mode == 1) {
         st_v4(dst1 + static_cast<size_t>(i) * 16, s);
+      } else {   // mode 2 (profiling only): this rank's partial straight to y, no exchange
+        const int c = (i % F4) * 4;
+        if (p.bias) {
+          const __nv_bfloat16* bp = p.bias + ht * BH + c;
+          s.x += __bfloat162float(bp[0]); s.y += __bfloat162float(bp[1]);
+          s.z += __bfloat162float(bp[2]); s.w += __bfloat162float(bp[3]);
+        }
+        st_v2u(p.y + static_cast<int64_t>(tok0 + i / F4) * p.y_stride + ht * BH + c, pack_bf16x2(s.x, s.y),
+               pack_bf16x2(s.z, s.w));
       }
     }
   }
   cluster_arrive();   // this CTA no longer reads its peers' shared memory (waited for before exit)
   const size_t flag_off = RP_HDR_BYTES + (static_cast<size_t>(p.rank * p.ksplit + ks) * RP_MAX_TILES + tile) * 4;
-  if (has_rows) {
+  if (has_rows && p.mode != 2) {
     // the release below is cumulative over the CTA barrier: it orders every thread's pushed stores before the flag
     __syncthreads();
     if (p.mode == 0) {
@@ -258,7 +270,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 
   // ---------------- 3. reduce over ranks ----------------
   const int col0 = ht * BH;
-  if (has_rows && (p.mode == 0 || owner == p.rank)) {
+  if (has_rows && (p.mode == 0 || (p.mode == 1 && owner == p.rank))) {
     if (tid < p.world)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES +
                                                   (static_cast<size_t>(tid * p.ksplit + ks) * RP_MAX_TILES + tile) * 4),
@@ -293,7 +305,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
                                                    (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4), epoch);
     }
   }
-  if (has_rows && p.mode != 0) {
+  if (has_rows && p.mode == 1) {
     if (tid == 0)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + RP_FLAG1_BYTES +
                                                   (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4),
@@ -321,37 +333,53 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 
 // ---- host side ---------------------------------------------------------------------------------------------
 struct RpPlan {
-  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, stages;
+  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, stages, bk;
   size_t smem, par_need, res_off;
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
+int g_force_bk = -1;   // tuning only: NVLLM_RP_BK=64|128 (read once)
 unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
 
 int rp_nt16(int n_tokens) { return n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15); }
 
 // Ring depth: as deep as lets two CTAs share an SM's shared memory (8 stages of a 16-token decode tile keep
 // 2 x 7 x 6 KB = 84 KB of loads in flight per SM).
-int rp_stages(int bh, int nt16) {
-  const size_t stage = size_t(bh + nt16) * 128, budget = size_t(100) * 1024;
-  return 8 * stage <= budget ? 8 : 6 * stage <= budget ? 6 : 4;
+constexpr size_t RP_SMEM_BUDGET = size_t(100) * 1024;   // per CTA: two CTAs share an SM
+
+int rp_stages(int bh, int nt16, int bk) {
+  const size_t stage = size_t(bh + nt16) * bk * 2;
+  return 8 * stage <= RP_SMEM_BUDGET ? 8 : 6 * stage <= RP_SMEM_BUDGET ? 6 : 4;
 }
 
-size_t rp_smem_bytes(int bh, int n_tokens) {
+// 256-byte rows per stage (longer contiguous runs per W row) whenever a 4-deep ring of them still fits
+int rp_bk(int bh, int nt16, int k_per_rank) {
+  if (g_force_bk < 0) {
+    const char* e = getenv("NVLLM_RP_BK");
+    g_force_bk = e ? atoi(e) : 0;
+  }
+  if (g_force_bk == 64) return 64;
+  const bool fits = 4 * size_t(bh + nt16) * 256 <= RP_SMEM_BUDGET && k_per_rank % 128 == 0;
+  return fits ? 128 : 64;
+}
+
+size_t rp_smem_bytes(int bh, int n_tokens, int bk) {
   const int nt16 = rp_nt16(n_tokens);
-  const size_t ring = size_t(rp_stages(bh, nt16)) * (size_t(bh) + nt16) * 128;
+  const size_t ring = size_t(rp_stages(bh, nt16, bk)) * (size_t(bh) + nt16) * bk * 2;
   const size_t epi = size_t(nt16) * (bh + 8) * 4;
   return ring > epi ? ring : epi;
 }
 
-const void* rp_kernel(int bh, int stages) {
-  if (bh == 32)
-    return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 8>)
-           : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 6>)
-                         : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<32, 4>);
-  return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 8>)
-         : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 6>)
-                       : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<64, 4>);
+template <int BH, int BK>
+const void* rp_kernel_s(int stages) {
+  return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 8, BK>)
+         : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 6, BK>)
+                       : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 4, BK>);
+}
+
+const void* rp_kernel(int bh, int stages, int bk) {
+  if (bh == 32) return bk == 128 ? rp_kernel_s<32, 128>(stages) : rp_kernel_s<32, 64>(stages);
+  return bk == 128 ? rp_kernel_s<64, 128>(stages) : rp_kernel_s<64, 64>(stages);
 }
 
 // Load every instantiation on the current device and opt it into large dynamic shared memory, so that the first
@@ -365,12 +393,13 @@ cudaError_t rp_warm_device() {
   if (e != cudaSuccess) return e;
   if (dev < 64 && done[dev]) return cudaSuccess;
   for (int bh = 32; bh <= 64; bh += 32)
-    for (int st = 4; st <= 8; st += 2) {
-      cudaFuncAttributes fa;
-      e = cudaFuncSetAttribute(rp_kernel(bh, st), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
-      if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, st));
-      if (e != cudaSuccess) return e;
-    }
+    for (int st = 4; st <= 8; st += 2)
+      for (int bk = 64; bk <= 128; bk += 64) {
+        cudaFuncAttributes fa;
+        e = cudaFuncSetAttribute(rp_kernel(bh, st, bk), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, st, bk));
+        if (e != cudaSuccess) return e;
+      }
   if (dev < 64) done[dev] = true;
   return cudaSuccess;
 }
@@ -393,13 +422,13 @@ void rp_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int n_
 // Co-resident cluster capacity of the current device for (feature tile, token bucket, cluster size).  Cached, so a
 // call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA runtime call besides the
 // launch itself.
-int rp_max_clusters(int bh, int nt16, int stages, size_t smem, int ksplit, int* out) {
-  static int cache[64][2][RP_TOKB / 16 + 1][4] = {};
+int rp_max_clusters(int bh, int nt16, int stages, int bk, size_t smem, int ksplit, int* out) {
+  static int cache[64][2][2][RP_TOKB / 16 + 1][4] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return record_cuda_error(e);
   const int lg = ksplit == 1 ? 0 : ksplit == 2 ? 1 : ksplit == 4 ? 2 : 3;
-  int* slot = dev < 64 ? &cache[dev][bh == 64][nt16 / 16][lg] : nullptr;
+  int* slot = dev < 64 ? &cache[dev][bh == 64][bk == 128][nt16 / 16][lg] : nullptr;
   if (slot && *slot > 0) {
     *out = *slot;
     return NVLLM_OK;
@@ -410,7 +439,7 @@ int rp_max_clusters(int bh, int nt16, int stages, size_t smem, int ksplit, int* 
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, RP_PLAN_CAP / ksplit * ksplit, ksplit, smem, nullptr);
   int n = 0;
-  e = cudaOccupancyMaxActiveClusters(&n, rp_kernel(bh, stages), &cfg);
+  e = cudaOccupancyMaxActiveClusters(&n, rp_kernel(bh, stages, bk), &cfg);
   if (e != cudaSuccess) return record_cuda_error(e);
   *out = n;
   if (slot) *slot = n;
@@ -423,7 +452,7 @@ int rp_max_clusters(int bh, int nt16, int stages, size_t smem, int ksplit, int* 
 // homogeneous node; the inbox layout does not depend on the k split).
 int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* pl) {
   if (n_tokens <= 0 || n_tokens > RP_MAX_TOKENS || world < 2 || world > RP_MAX_WORLD) return NVLLM_ERR_UNSUPPORTED;
-  if (k_per_rank <= 0 || k_per_rank % RP_BK || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
+  if (k_per_rank <= 0 || k_per_rank % RP_BK_MIN || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
   const int tok_blocks = (n_tokens + RP_TOKB - 1) / RP_TOKB;
   const int cap = RP_PLAN_CAP;
   // 64-feature tiles once the x tile (re-read by every feature tile) outweighs the W tile
@@ -433,21 +462,25 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
   int ksplit = 1;
   for (int c = 2; c <= RP_MAX_KSPLIT; c *= 2) {
-    if (k_per_rank % (c * RP_BK) || k_per_rank / c < 256 || n_tiles * c > cap) break;
+    if (k_per_rank % (c * RP_BK_MIN) || k_per_rank / c < 256 || n_tiles * c > cap) break;
     ksplit = c;
   }
   if (g_force_ksplit > 0) {
     ksplit = g_force_ksplit;
-    if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
+    if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK_MIN) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
   }
+  const int nt16 = rp_nt16(n_tokens);
+  int bk = rp_bk(bh, nt16, k_per_rank);
+  if ((k_per_rank / ksplit) % bk) bk = 64;
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
   const size_t pushed = size_t(world - 1) * n_tokens * out_features * 4;
   int mode = pushed <= (size_t(4) << 20) ? 0 : 1;
-  if (g_force_mode == 0 || g_force_mode == 1) mode = g_force_mode;
+  if (g_force_mode >= 0 && g_force_mode <= 2) mode = g_force_mode;
   pl->bh = bh; pl->ksplit = ksplit; pl->mode = mode; pl->h_tiles = h_tiles; pl->tok_blocks = tok_blocks;
   pl->n_tiles = n_tiles; pl->kc = k_per_rank / ksplit;
-  pl->stages = rp_stages(bh, rp_nt16(n_tokens));
-  pl->smem = rp_smem_bytes(bh, n_tokens);
+  pl->bk = bk;
+  pl->stages = rp_stages(bh, nt16, bk);
+  pl->smem = rp_smem_bytes(bh, n_tokens, bk);
   pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);   // one inbox slot per rank
   pl->par_need = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
   return NVLLM_OK;
@@ -557,7 +590,7 @@ int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* err
 int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit, int32_t mode, int64_t timeout_ms) {
   if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64)) return NVLLM_ERR_BAD_ARG;
   if (ksplit < 0 || ksplit > RP_MAX_KSPLIT || (ksplit & (ksplit - 1))) return NVLLM_ERR_BAD_ARG;
-  if (mode < -1 || mode > 1) return NVLLM_ERR_BAD_ARG;
+  if (mode < -1 || mode > 2) return NVLLM_ERR_BAD_ARG;   // 2: local partial only (profiling)
   g_force_bh = feature_tile;
   g_force_ksplit = ksplit;
   g_force_mode = mode;
@@ -598,7 +631,7 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   const int nt16 = rp_nt16(n_tokens);
   for (;;) {
     int max_clusters = 0;
-    st = rp_max_clusters(pl.bh, nt16, pl.stages, pl.smem, pl.ksplit, &max_clusters);
+    st = rp_max_clusters(pl.bh, nt16, pl.stages, pl.bk, pl.smem, pl.ksplit, &max_clusters);
     if (st != NVLLM_OK) return st;
     if (pl.n_tiles <= max_clusters) break;
     if (pl.ksplit == 1 || g_force_ksplit > 0) return NVLLM_ERR_UNSUPPORTED;
@@ -625,7 +658,7 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, pl.n_tiles * pl.ksplit, pl.ksplit, pl.smem, static_cast<cudaStream_t>(stream));
   void* args[] = {&p};
-  const cudaError_t le = cudaLaunchKernelExC(&cfg, rp_kernel(pl.bh, pl.stages), args);
+  const cudaError_t le = cudaLaunchKernelExC(&cfg, rp_kernel(pl.bh, pl.stages, pl.bk), args);
   if (le != cudaSuccess) return record_cuda_error(le);
   note_launch();
   return record_cuda_error(cudaGetLastError());

@@ -72,7 +72,7 @@ def test_comm_bytes_and_plan_are_host_arithmetic(lib):
     # forcing is validated
     assert lib.nvllm_rowparallel_set_plan(48, 0, -1, 0) == 1
     assert lib.nvllm_rowparallel_set_plan(0, 3, -1, 0) == 1
-    assert lib.nvllm_rowparallel_set_plan(0, 0, 2, 0) == 1
+    assert lib.nvllm_rowparallel_set_plan(0, 0, 3, 0) == 1   # 2 is the local-partial profiling mode
     assert lib.nvllm_rowparallel_set_plan(64, 2, 1, 0) == 0
     assert lib.nvllm_rowparallel_plan(16, 1024, 1024, 2, ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)) == 0
     assert (bh.value, ks.value, mode.value) == (64, 2, 1)
