@@ -102,9 +102,19 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;\n" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;\n" ::: "memory"); }
 
-template <int BH, int STAGES, int BK>
+// Ring depth: as deep as lets two CTAs share an SM's shared memory (RP_SMEM_BUDGET each).
+constexpr size_t RP_SMEM_BUDGET = size_t(100) * 1024;
+__host__ __device__ constexpr int rp_stages(int bh, int mt, int bk) {
+  const size_t stage = size_t(bh + mt * 16) * bk * 2;
+  return 8 * stage <= RP_SMEM_BUDGET ? 8 : 6 * stage <= RP_SMEM_BUDGET ? 6 : 4;
+}
+
+// BH output features x (MT*16) token rows per CTA, BK k elements per pipeline stage.
+template <int BH, int BK, int MT>
 __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int STAGES = rp_stages(BH, MT, BK);
+  constexpr int NT = MT * 16;             // staged token rows (rows past the last token are zero-filled)
   constexpr int NJ = BH / 32;             // 8-feature n-tiles per warp (4 warps split the BH features)
   constexpr int F4 = BH / 4;              // float4 chunks per tile row
   constexpr int EP_STRIDE = BH + 8;       // floats per staged epilogue row (padding breaks bank conflicts)
@@ -116,9 +126,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   const int tile = blockIdx.x / p.ksplit;
   const int ht = tile % p.h_tiles;
   const int tok0 = (tile / p.h_tiles) * RP_TOKB;
-  const int nt = min(RP_TOKB, p.n_tokens - tok0);
-  const int nt16 = (nt + 15) & ~15;
-  const int mt = nt16 >> 4;
+  const int nt = min(min(RP_TOKB, NT), p.n_tokens - tok0);
 
   uint8_t* const local = p.comm[p.rank];
   RpControl* const ctrl = reinterpret_cast<RpControl*>(local);
@@ -128,34 +136,45 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   // ---------------- 1. partial GEMM over k in [ks*kc, (ks+1)*kc) ----------------
   constexpr int ROWB = BK * 2;            // bytes per staged row
   constexpr int CPR = BK / 8;             // 16-byte chunks per staged row; chunks are XOR-swizzled by (row & 7)
-  const uint32_t w_stage = BH * ROWB, x_stage = nt16 * ROWB, stage_bytes = w_stage + x_stage;
+  constexpr int RSTEP = RP_THREADS / CPR; // a thread keeps its chunk column and walks rows r0, r0+RSTEP, ... (RSTEP % 8 == 0)
+  constexpr uint32_t W_STAGE = BH * ROWB, STAGE_BYTES = (BH + NT) * ROWB;
   const uint32_t sbase = smem_u32(smem);
-  const __nv_bfloat16* wsrc = p.w + static_cast<int64_t>(ht) * BH * p.w_stride + static_cast<int64_t>(ks) * p.kc;
-  const __nv_bfloat16* xsrc = p.x + static_cast<int64_t>(tok0) * p.x_stride + static_cast<int64_t>(ks) * p.kc;
   const int nk = p.kc / BK;
+  // per-thread copy assignments, fixed for the whole k loop: only the k offset moves
+  const int r0 = tid / CPR, ch0 = tid % CPR;
+  const uint32_t dst0 = r0 * ROWB + ((ch0 ^ (r0 & 7)) << 4);
+  const __nv_bfloat16* const wsrc0 = p.w + (static_cast<int64_t>(ht) * BH + r0) * p.w_stride +
+                                     static_cast<int64_t>(ks) * p.kc + ch0 * 8;
+  const __nv_bfloat16* const xbase = p.x + static_cast<int64_t>(tok0) * p.x_stride + static_cast<int64_t>(ks) * p.kc + ch0 * 8;
+  const __nv_bfloat16* const xsrc0 = xbase + static_cast<int64_t>(r0) * p.x_stride;
+  const int64_t w_step = static_cast<int64_t>(RSTEP) * p.w_stride, x_step = static_cast<int64_t>(RSTEP) * p.x_stride;
 
   auto load_stage = [&](int i) {
-    const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
-    const __nv_bfloat16* ws = wsrc + i * BK;
-    const __nv_bfloat16* xs = xsrc + i * BK;
-    for (int c = tid; c < BH * CPR; c += RP_THREADS) {
-      const int row = c / CPR, ch = c % CPR;
-      cp_async16(wb + row * ROWB + ((ch ^ (row & 7)) << 4), ws + row * p.w_stride + ch * 8, 16);
-    }
-    for (int c = tid; c < nt16 * CPR; c += RP_THREADS) {
-      const int row = c / CPR, ch = c % CPR;
-      const bool ok = row < nt;   // rows past the last token are zero-filled
-      cp_async16(xb + row * ROWB + ((ch ^ (row & 7)) << 4), xs + (ok ? row : 0) * p.x_stride + ch * 8, ok ? 16 : 0);
+    const uint32_t wb = sbase + (i % STAGES) * STAGE_BYTES + dst0, xb = wb + W_STAGE;
+    const __nv_bfloat16* ws = wsrc0 + i * BK;
+    const __nv_bfloat16* xs = xsrc0 + i * BK;
+#pragma unroll
+    for (int j = 0; j < BH / RSTEP; ++j) cp_async16(wb + j * (RSTEP * ROWB), ws + j * w_step, 16);
+#pragma unroll
+    for (int j = 0; j < NT / RSTEP; ++j) {
+      const bool ok = r0 + j * RSTEP < nt;
+      cp_async16(xb + j * (RSTEP * ROWB), ok ? xs + j * x_step : xbase, ok ? 16 : 0);
     }
   };
 
-  float acc[8][NJ][4];
+  float acc[MT][NJ][4];
 #pragma unroll
-  for (int m = 0; m < 8; ++m)
+  for (int m = 0; m < MT; ++m)
 #pragma unroll
     for (int j = 0; j < NJ; ++j)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+
+  // ldmatrix lane addresses inside a stage (the k16 step only flips chunk bits: XOR with a constant)
+  const int brow = warp * (BH / 4) + (lane & 7);
+  const uint32_t boff = brow * ROWB, bsw = ((lane >> 3) ^ (brow & 7)) << 4;          // chunk kk2*4 + (lane>>3)
+  const int arow = lane & 15;
+  const uint32_t aoff = W_STAGE + arow * ROWB, asw = ((lane >> 4) ^ (arow & 7)) << 4;  // chunk kk*2 + (lane>>4)
 
 #pragma unroll
   for (int s = 0; s < STAGES - 1; ++s) {
@@ -167,46 +186,39 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     __syncthreads();   // stage i landed for every thread; stage i-1 is no longer being read
     if (i + STAGES - 1 < nk) load_stage(i + STAGES - 1);
     cp_async_commit();
-    const uint32_t wb = sbase + (i % STAGES) * stage_bytes, xb = wb + w_stage;
+    const uint32_t sb = sbase + (i % STAGES) * STAGE_BYTES;
 #pragma unroll
     for (int kk2 = 0; kk2 < BK / 32; ++kk2) {
       uint32_t b[NJ][4];   // {b0,b1} of k16 step 2*kk2, {b0,b1} of step 2*kk2+1
 #pragma unroll
-      for (int j = 0; j < NJ; ++j) {
-        const int row = warp * (BH / 4) + j * 8 + (lane & 7), ch = kk2 * 4 + (lane >> 3);
-        ldmatrix_x4(b[j][0], b[j][1], b[j][2], b[j][3], wb + row * ROWB + ((ch ^ (row & 7)) << 4));
-      }
+      for (int j = 0; j < NJ; ++j)
+        ldmatrix_x4(b[j][0], b[j][1], b[j][2], b[j][3], sb + boff + j * (8 * ROWB) + (bsw ^ ((kk2 * 4) << 4)));
 #pragma unroll
       for (int kh = 0; kh < 2; ++kh) {
         const int kk = kk2 * 2 + kh;
 #pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          if (m < mt) {
-            uint32_t a0, a1, a2, a3;
-            const int row = m * 16 + (lane & 15), ch = kk * 2 + (lane >> 4);
-            ldmatrix_x4(a0, a1, a2, a3, xb + row * ROWB + ((ch ^ (row & 7)) << 4));
+        for (int m = 0; m < MT; ++m) {
+          uint32_t a0, a1, a2, a3;
+          ldmatrix_x4(a0, a1, a2, a3, sb + aoff + m * (16 * ROWB) + (asw ^ ((kk * 2) << 4)));
 #pragma unroll
-            for (int j = 0; j < NJ; ++j) mma_bf16_16816(acc[m][j], a0, a1, a2, a3, b[j][2 * kh], b[j][2 * kh + 1]);
-          }
+          for (int j = 0; j < NJ; ++j) mma_bf16_16816(acc[m][j], a0, a1, a2, a3, b[j][2 * kh], b[j][2 * kh + 1]);
         }
       }
     }
   }
   cp_async_wait<0>();
-  __syncthreads();   // the ring is free: reuse it to stage the fp32 tile [nt16][EP_STRIDE]
+  __syncthreads();   // the ring is free: reuse it to stage the fp32 tile [NT][EP_STRIDE]
 
   float* const ep = reinterpret_cast<float*>(smem);
   {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-    for (int m = 0; m < 8; ++m) {
-      if (m < mt) {
+    for (int m = 0; m < MT; ++m) {
 #pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-          const int col = warp * (BH / 4) + j * 8 + 2 * t;
-          *reinterpret_cast<float2*>(ep + (m * 16 + g) * EP_STRIDE + col) = make_float2(acc[m][j][0], acc[m][j][1]);
-          *reinterpret_cast<float2*>(ep + (m * 16 + g + 8) * EP_STRIDE + col) = make_float2(acc[m][j][2], acc[m][j][3]);
-        }
+      for (int j = 0; j < NJ; ++j) {
+        const int col = warp * (BH / 4) + j * 8 + 2 * t;
+        *reinterpret_cast<float2*>(ep + (m * 16 + g) * EP_STRIDE + col) = make_float2(acc[m][j][0], acc[m][j][1]);
+        *reinterpret_cast<float2*>(ep + (m * 16 + g + 8) * EP_STRIDE + col) = make_float2(acc[m][j][2], acc[m][j][3]);
       }
     }
   }
@@ -333,7 +345,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 
 // ---- host side ---------------------------------------------------------------------------------------------
 struct RpPlan {
-  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, stages, bk;
+  int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, mt, bk;
   size_t smem, par_need, res_off;
 };
 
@@ -343,43 +355,39 @@ unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
 
 int rp_nt16(int n_tokens) { return n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15); }
 
-// Ring depth: as deep as lets two CTAs share an SM's shared memory (8 stages of a 16-token decode tile keep
-// 2 x 7 x 6 KB = 84 KB of loads in flight per SM).
-constexpr size_t RP_SMEM_BUDGET = size_t(100) * 1024;   // per CTA: two CTAs share an SM
-
-int rp_stages(int bh, int nt16, int bk) {
-  const size_t stage = size_t(bh + nt16) * bk * 2;
-  return 8 * stage <= RP_SMEM_BUDGET ? 8 : 6 * stage <= RP_SMEM_BUDGET ? 6 : 4;
+int rp_mt(int n_tokens) {   // 16-row MMA tiles per CTA: 1, 2, 4 or 8 (bucketed so the kernel loops are static)
+  const int nt16 = rp_nt16(n_tokens);
+  return nt16 <= 16 ? 1 : nt16 <= 32 ? 2 : nt16 <= 64 ? 4 : 8;
 }
 
-// 256-byte rows per stage (longer contiguous runs per W row) whenever a 4-deep ring of them still fits
-int rp_bk(int bh, int nt16, int k_per_rank) {
+// 256-byte rows per stage (longer contiguous runs per W row, fewer barriers) whenever a 4-deep ring of them fits
+int rp_bk(int bh, int mt, int k_per_rank) {
   if (g_force_bk < 0) {
     const char* e = getenv("NVLLM_RP_BK");
     g_force_bk = e ? atoi(e) : 0;
   }
   if (g_force_bk == 64) return 64;
-  const bool fits = 4 * size_t(bh + nt16) * 256 <= RP_SMEM_BUDGET && k_per_rank % 128 == 0;
+  const bool fits = 4 * size_t(bh + mt * 16) * 256 <= RP_SMEM_BUDGET && k_per_rank % 128 == 0;
   return fits ? 128 : 64;
 }
 
-size_t rp_smem_bytes(int bh, int n_tokens, int bk) {
-  const int nt16 = rp_nt16(n_tokens);
-  const size_t ring = size_t(rp_stages(bh, nt16, bk)) * (size_t(bh) + nt16) * bk * 2;
-  const size_t epi = size_t(nt16) * (bh + 8) * 4;
+size_t rp_smem_bytes(int bh, int mt, int bk) {
+  const size_t ring = size_t(rp_stages(bh, mt, bk)) * (size_t(bh) + mt * 16) * bk * 2;
+  const size_t epi = size_t(mt) * 16 * (bh + 8) * 4;
   return ring > epi ? ring : epi;
 }
 
 template <int BH, int BK>
-const void* rp_kernel_s(int stages) {
-  return stages == 8   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 8, BK>)
-         : stages == 6 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 6, BK>)
-                       : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, 4, BK>);
+const void* rp_kernel_m(int mt) {
+  return mt == 1   ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, BK, 1>)
+         : mt == 2 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, BK, 2>)
+         : mt == 4 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, BK, 4>)
+                   : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<BH, BK, 8>);
 }
 
-const void* rp_kernel(int bh, int stages, int bk) {
-  if (bh == 32) return bk == 128 ? rp_kernel_s<32, 128>(stages) : rp_kernel_s<32, 64>(stages);
-  return bk == 128 ? rp_kernel_s<64, 128>(stages) : rp_kernel_s<64, 64>(stages);
+const void* rp_kernel(int bh, int bk, int mt) {
+  if (bh == 32) return bk == 128 ? rp_kernel_m<32, 128>(mt) : rp_kernel_m<32, 64>(mt);
+  return bk == 128 ? rp_kernel_m<64, 128>(mt) : rp_kernel_m<64, 64>(mt);
 }
 
 // Load every instantiation on the current device and opt it into large dynamic shared memory, so that the first
@@ -393,11 +401,12 @@ cudaError_t rp_warm_device() {
   if (e != cudaSuccess) return e;
   if (dev < 64 && done[dev]) return cudaSuccess;
   for (int bh = 32; bh <= 64; bh += 32)
-    for (int st = 4; st <= 8; st += 2)
+    for (int mt = 1; mt <= 8; mt *= 2)
       for (int bk = 64; bk <= 128; bk += 64) {
+        if (rp_smem_bytes(bh, mt, bk) > RP_SMEM_BUDGET) continue;   // never planned
         cudaFuncAttributes fa;
-        e = cudaFuncSetAttribute(rp_kernel(bh, st, bk), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
-        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, st, bk));
+        e = cudaFuncSetAttribute(rp_kernel(bh, bk, mt), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, bk, mt));
         if (e != cudaSuccess) return e;
       }
   if (dev < 64) done[dev] = true;
@@ -422,13 +431,13 @@ void rp_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int n_
 // Co-resident cluster capacity of the current device for (feature tile, token bucket, cluster size).  Cached, so a
 // call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA runtime call besides the
 // launch itself.
-int rp_max_clusters(int bh, int nt16, int stages, int bk, size_t smem, int ksplit, int* out) {
-  static int cache[64][2][2][RP_TOKB / 16 + 1][4] = {};
+int rp_max_clusters(int bh, int mt, int bk, size_t smem, int ksplit, int* out) {
+  static int cache[64][2][2][4][4] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return record_cuda_error(e);
   const int lg = ksplit == 1 ? 0 : ksplit == 2 ? 1 : ksplit == 4 ? 2 : 3;
-  int* slot = dev < 64 ? &cache[dev][bh == 64][bk == 128][nt16 / 16][lg] : nullptr;
+  int* slot = dev < 64 ? &cache[dev][bh == 64][bk == 128][mt == 1 ? 0 : mt == 2 ? 1 : mt == 4 ? 2 : 3][lg] : nullptr;
   if (slot && *slot > 0) {
     *out = *slot;
     return NVLLM_OK;
@@ -439,7 +448,7 @@ int rp_max_clusters(int bh, int nt16, int stages, int bk, size_t smem, int kspli
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, RP_PLAN_CAP / ksplit * ksplit, ksplit, smem, nullptr);
   int n = 0;
-  e = cudaOccupancyMaxActiveClusters(&n, rp_kernel(bh, stages, bk), &cfg);
+  e = cudaOccupancyMaxActiveClusters(&n, rp_kernel(bh, bk, mt), &cfg);
   if (e != cudaSuccess) return record_cuda_error(e);
   *out = n;
   if (slot) *slot = n;
@@ -469,8 +478,8 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
     ksplit = g_force_ksplit;
     if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK_MIN) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
   }
-  const int nt16 = rp_nt16(n_tokens);
-  int bk = rp_bk(bh, nt16, k_per_rank);
+  const int mt = rp_mt(n_tokens);
+  int bk = rp_bk(bh, mt, k_per_rank);
   if ((k_per_rank / ksplit) % bk) bk = 64;
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
   const size_t pushed = size_t(world - 1) * n_tokens * out_features * 4;
@@ -479,8 +488,8 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   pl->bh = bh; pl->ksplit = ksplit; pl->mode = mode; pl->h_tiles = h_tiles; pl->tok_blocks = tok_blocks;
   pl->n_tiles = n_tiles; pl->kc = k_per_rank / ksplit;
   pl->bk = bk;
-  pl->stages = rp_stages(bh, nt16, bk);
-  pl->smem = rp_smem_bytes(bh, n_tokens, bk);
+  pl->mt = mt;
+  pl->smem = rp_smem_bytes(bh, mt, bk);
   pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);   // one inbox slot per rank
   pl->par_need = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
   return NVLLM_OK;
@@ -628,10 +637,9 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
 
   // every CTA of the grid must be co-resident (cross-rank waits inside the kernel): shrink the cluster while the
   // device cannot hold all of them at once
-  const int nt16 = rp_nt16(n_tokens);
   for (;;) {
     int max_clusters = 0;
-    st = rp_max_clusters(pl.bh, nt16, pl.stages, pl.bk, pl.smem, pl.ksplit, &max_clusters);
+    st = rp_max_clusters(pl.bh, pl.mt, pl.bk, pl.smem, pl.ksplit, &max_clusters);
     if (st != NVLLM_OK) return st;
     if (pl.n_tiles <= max_clusters) break;
     if (pl.ksplit == 1 || g_force_ksplit > 0) return NVLLM_ERR_UNSUPPORTED;
@@ -658,7 +666,7 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, pl.n_tiles * pl.ksplit, pl.ksplit, pl.smem, static_cast<cudaStream_t>(stream));
   void* args[] = {&p};
-  const cudaError_t le = cudaLaunchKernelExC(&cfg, rp_kernel(pl.bh, pl.stages, pl.bk), args);
+  const cudaError_t le = cudaLaunchKernelExC(&cfg, rp_kernel(pl.bh, pl.bk, pl.mt), args);
   if (le != cudaSuccess) return record_cuda_error(le);
   note_launch();
   return record_cuda_error(cudaGetLastError());
