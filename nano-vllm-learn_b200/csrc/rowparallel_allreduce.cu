@@ -26,6 +26,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <unordered_map>
 
 #include "common.cuh"
 
@@ -62,6 +63,7 @@ struct RpParams {
   int rank, world, n_tokens, ksplit, kc, h_tiles, n_tiles, mode;
   unsigned long long par_bytes;   // bytes of one parity's data area
   unsigned long long res_off;     // offset of the result area inside a parity (mode 1)
+  unsigned long long ll_off;      // offset of the flag-in-data inbox inside a parity (mode 3)
   unsigned long long timeout_ns;
 };
 
@@ -83,6 +85,15 @@ __device__ __forceinline__ void st_v4(void* p, const float4& v) {
 }
 __device__ __forceinline__ void st_v2u(void* p, uint32_t a, uint32_t b) {
   asm volatile("st.global.v2.u32 [%0], {%1,%2};\n" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+
+__device__ __forceinline__ void st_volatile_v4u(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ld_volatile_v4u(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
 }
 
 // Spin until *flag has reached `epoch` (wrap-safe); on timeout record the tile and give up.
@@ -236,6 +247,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   const int r_lo = min(nt, ks * rows_per), r_hi = min(nt, r_lo + rows_per);
   const bool has_rows = r_hi > r_lo;   // CTA-uniform, and the same on every rank
   const size_t inbox_off = par_off + (static_cast<size_t>(p.rank) * p.n_tiles + tile) * TILE_BYTES;
+  const size_t ll_off = par_off + p.ll_off + (static_cast<size_t>(p.rank) * p.n_tiles + tile) * (2 * TILE_BYTES);
   {
     const float* epc[RP_MAX_KSPLIT];
     cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
@@ -256,6 +268,14 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
         for (int d = 0; d < p.world; ++d) st_v4(p.comm[d] + inbox_off + static_cast<size_t>(i) * 16, s);
       } else if (p.mode == 1) {
         st_v4(dst1 + static_cast<size_t>(i) * 16, s);
+      } else if (p.mode == 3) {
+        // flag-in-data ("LL"): every 8 bytes carry 4 bytes of payload and the call epoch, so the receiver needs
+        // neither a separate flag nor a fence on this side -- an 8-byte half is valid as soon as its epoch matches
+        const size_t off = ll_off + static_cast<size_t>(i) * 32;
+        for (int d = 0; d < p.world; ++d) {
+          st_volatile_v4u(p.comm[d] + off, __float_as_uint(s.x), epoch, __float_as_uint(s.y), epoch);
+          st_volatile_v4u(p.comm[d] + off + 16, __float_as_uint(s.z), epoch, __float_as_uint(s.w), epoch);
+        }
       } else {   // mode 2 (profiling only): this rank's partial straight to y, no exchange
         const int c = (i % F4) * 4;
         if (p.bias) {
@@ -270,7 +290,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   }
   cluster_arrive();   // this CTA no longer reads its peers' shared memory (waited for before exit)
   const size_t flag_off = RP_HDR_BYTES + (static_cast<size_t>(p.rank * p.ksplit + ks) * RP_MAX_TILES + tile) * 4;
-  if (has_rows && p.mode != 2) {
+  if (has_rows && p.mode < 2) {
     // the release below is cumulative over the CTA barrier: it orders every thread's pushed stores before the flag
     __syncthreads();
     if (p.mode == 0) {
@@ -317,6 +337,50 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
                                                    (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4), epoch);
     }
   }
+  if (has_rows && p.mode == 3) {
+    const uint8_t* const in0 = local + par_off + p.ll_off + static_cast<size_t>(tile) * (2 * TILE_BYTES);
+    const size_t slot_stride = static_cast<size_t>(p.n_tiles) * (2 * TILE_BYTES);
+    for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
+      uint4 a[RP_MAX_WORLD], b[RP_MAX_WORLD];
+      unsigned long long t0 = 0;
+      for (int spins = 0;; ++spins) {
+        bool ready = true;
+#pragma unroll
+        for (int sl = 0; sl < RP_MAX_WORLD; ++sl) {
+          if (sl < p.world) {
+            const uint8_t* src = in0 + sl * slot_stride + static_cast<size_t>(i) * 32;
+            a[sl] = ld_volatile_v4u(src);
+            b[sl] = ld_volatile_v4u(src + 16);
+            ready = ready && a[sl].y == epoch && a[sl].w == epoch && b[sl].y == epoch && b[sl].w == epoch;
+          }
+        }
+        if (ready) break;
+        if ((spins & 63) == 63) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          if (now - t0 > p.timeout_ns) {
+            atomicCAS(&ctrl->error, 0u, 1u + static_cast<uint32_t>(tile));
+            break;
+          }
+        }
+      }
+      float4 s = make_float4(__uint_as_float(a[0].x), __uint_as_float(a[0].z), __uint_as_float(b[0].x), __uint_as_float(b[0].z));
+#pragma unroll
+      for (int sl = 1; sl < RP_MAX_WORLD; ++sl) {
+        if (sl < p.world) {
+          s.x += __uint_as_float(a[sl].x); s.y += __uint_as_float(a[sl].z);
+          s.z += __uint_as_float(b[sl].x); s.w += __uint_as_float(b[sl].z);
+        }
+      }
+      const int row = i / F4, c = (i % F4) * 4;
+      if (p.bias) {
+        const __nv_bfloat16* bp = p.bias + col0 + c;
+        s.x += __bfloat162float(bp[0]); s.y += __bfloat162float(bp[1]);
+        s.z += __bfloat162float(bp[2]); s.w += __bfloat162float(bp[3]);
+      }
+      st_v2u(p.y + static_cast<int64_t>(tok0 + row) * p.y_stride + col0 + c, pack_bf16x2(s.x, s.y), pack_bf16x2(s.z, s.w));
+    }
+  }
   if (has_rows && p.mode == 1) {
     if (tid == 0)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + RP_FLAG1_BYTES +
@@ -346,10 +410,11 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 // ---- host side ---------------------------------------------------------------------------------------------
 struct RpPlan {
   int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, mt, bk;
-  size_t smem, par_need, res_off;
+  size_t smem, par_need, res_off, ll_off;
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
+std::unordered_map<void*, size_t> g_comm_bytes;   // buffers from nvllm_tp_comm_alloc (reset clears them whole)
 int g_force_bk = -1;   // tuning only: NVLLM_RP_BK=64|128 (read once)
 unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
 
@@ -483,15 +548,20 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   if ((k_per_rank / ksplit) % bk) bk = 64;
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
   const size_t pushed = size_t(world - 1) * n_tokens * out_features * 4;
-  int mode = pushed <= (size_t(4) << 20) ? 0 : 1;
-  if (g_force_mode >= 0 && g_force_mode <= 2) mode = g_force_mode;
+  // flag-in-data while the payload is small (it doubles the bytes but drops a fence + flag round trip), plain
+  // one-shot up to 4 MiB, then reduce-scatter + all-gather
+  int mode = pushed <= (size_t(1) << 20) ? 3 : pushed <= (size_t(4) << 20) ? 0 : 1;
+  if (g_force_mode >= 0 && g_force_mode <= 3) mode = g_force_mode;
   pl->bh = bh; pl->ksplit = ksplit; pl->mode = mode; pl->h_tiles = h_tiles; pl->tok_blocks = tok_blocks;
   pl->n_tiles = n_tiles; pl->kc = k_per_rank / ksplit;
   pl->bk = bk;
   pl->mt = mt;
   pl->smem = rp_smem_bytes(bh, mt, bk);
-  pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);   // one inbox slot per rank
-  pl->par_need = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
+  // one parity: [fp32 inbox, one slot per rank | bf16 result area (mode 1) | flag-in-data inbox (mode 3)]; the
+  // mode-3 area never holds anything but {payload, epoch} words, so a stale word cannot pass for a current one
+  pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);
+  pl->ll_off = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
+  pl->par_need = pl->ll_off + 2 * pl->res_off;
   return NVLLM_OK;
 }
 
@@ -527,7 +597,7 @@ int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out) {
   if (e != cudaSuccess) return record_cuda_error(e);
   e = cudaMalloc(&p, bytes);
   if (e != cudaSuccess) return record_cuda_error(e);
-  e = cudaMemset(p, 0, RP_DATA_OFF);   // epoch 0, flags 0; the data areas need no initial value
+  e = cudaMemset(p, 0, bytes);   // epoch 0, flags 0, and no word of the flag-in-data inboxes may look like an epoch
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e == cudaSuccess && ipc_handle_out) {
     cudaIpcMemHandle_t h;
@@ -539,6 +609,7 @@ int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out) {
     return record_cuda_error(e);
   }
   *dev_ptr = p;
+  g_comm_bytes[p] = bytes;
   return NVLLM_OK;
 }
 
@@ -560,6 +631,7 @@ int nvllm_tp_comm_close(void* peer_ptr) {
 
 int nvllm_tp_comm_free(void* dev_ptr) {
   if (!dev_ptr) return NVLLM_OK;
+  g_comm_bytes.erase(dev_ptr);
   return record_cuda_error(cudaFree(dev_ptr));
 }
 
@@ -567,7 +639,11 @@ int nvllm_tp_comm_reset(void* dev_ptr, void* stream) {
   if (!dev_ptr) return NVLLM_ERR_BAD_ARG;
   const cudaError_t e = rp_warm_device();
   if (e != cudaSuccess) return record_cuda_error(e);
-  return record_cuda_error(cudaMemsetAsync(dev_ptr, 0, RP_DATA_OFF, static_cast<cudaStream_t>(stream)));
+  // buffers of our own are cleared whole (the flag-in-data inboxes must not keep words of an earlier epoch count);
+  // for memory allocated elsewhere the caller zeroes the data area itself before this call
+  const auto it = g_comm_bytes.find(dev_ptr);
+  const size_t n = it != g_comm_bytes.end() ? it->second : RP_DATA_OFF;
+  return record_cuda_error(cudaMemsetAsync(dev_ptr, 0, n, static_cast<cudaStream_t>(stream)));
 }
 
 int nvllm_tp_comm_enable_peer(int32_t peer_device) {
@@ -599,7 +675,7 @@ int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* err
 int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit, int32_t mode, int64_t timeout_ms) {
   if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64)) return NVLLM_ERR_BAD_ARG;
   if (ksplit < 0 || ksplit > RP_MAX_KSPLIT || (ksplit & (ksplit - 1))) return NVLLM_ERR_BAD_ARG;
-  if (mode < -1 || mode > 2) return NVLLM_ERR_BAD_ARG;   // 2: local partial only (profiling)
+  if (mode < -1 || mode > 3) return NVLLM_ERR_BAD_ARG;   // 2: local partial only (profiling), 3: flag-in-data
   g_force_bh = feature_tile;
   g_force_ksplit = ksplit;
   g_force_mode = mode;
@@ -661,6 +737,7 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   p.h_tiles = pl.h_tiles; p.n_tiles = pl.n_tiles; p.mode = pl.mode;
   p.par_bytes = (comm_bytes - RP_DATA_OFF) / 2 / 16 * 16;
   p.res_off = pl.res_off;
+  p.ll_off = pl.ll_off;
   p.timeout_ns = g_timeout_ns;
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr;

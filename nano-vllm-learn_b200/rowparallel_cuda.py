@@ -7,7 +7,7 @@ straight into the peers' inboxes and reduce what arrives, so one launch replaces
 
 `TPComm` owns the peer-mapped buffers: one cudaMalloc per rank, exchanged between the rank PROCESSES (the reference
 spawns one process per GPU, llm_engine.py:29-36) as CUDA IPC handles through the existing process group.  Batches
-above `MAX_TOKENS` (long prefill: GEMM-bound, the collective is bandwidth- not latency-bound) keep the reference's
+above `ENGINE_MAX_TOKENS` (prefill: GEMM-bound, the collective is bandwidth- not latency-bound) keep the reference's
 own F.linear + dist.all_reduce.  No CPU path: CUDA tensors and the built library are required.
 """
 from __future__ import annotations
@@ -20,6 +20,10 @@ import torch
 from . import _lib, ops
 
 MAX_TOKENS = 512          # nvllm_rowparallel_linear_allreduce's n_tokens limit (include/nvllm_attn.h (6))
+# Batches the engine hands to the fused kernel.  Measured on 2 and 4 B200s (profiles/r01_rowparallel_tp{2,4}_v3_*.jsonl):
+# 1.3-1.9x cuBLAS + NCCL up to 64 tokens on every shard shape, about parity at 128-256 on Qwen3-0.6B shards and slower
+# on 8B-shape shards, slower at 512 — so larger batches keep the reference's own forward.
+ENGINE_MAX_TOKENS = int(os.environ.get("NVLLM_FUSED_ALLREDUCE_MAX_TOKENS", "64"))
 _IPC_HANDLE_BYTES = 64
 
 
@@ -97,6 +101,7 @@ class TPComm:
         buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
         hdl = symm_mem.rendezvous(buf, group)
         ptrs = [int(p) for p in hdl.buffer_ptrs]
+        buf.zero_()   # the flag-in-data inboxes must not hold anything that looks like a call epoch
         _lib.check(_lib.load().nvllm_tp_comm_reset(ctypes.c_void_p(ptrs[rank]), None), "tp_comm_reset")
         torch.cuda.synchronize()
         dist.barrier(group=group)
@@ -191,7 +196,7 @@ def install(RowParallelLinear) -> None:
             _SHAPES.add((self.input_size_per_partition, self.output_size))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > MAX_TOKENS or \
+        if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > min(MAX_TOKENS, ENGINE_MAX_TOKENS) or \
                 x.dtype != torch.bfloat16 or not x.is_cuda:
             return ref_forward(self, x)
         return ops.rowparallel_linear_allreduce(x, self.weight, self.bias, get_comm())

@@ -85,7 +85,7 @@ def _check(ys, xs, ws, bias, comms, what):
 
 
 @pytest.mark.parametrize("name", [n for n, c in cases.ROWPARALLEL_CASES.items() if c[4] == 2])
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 3])
 def test_cases_vs_oracle_and_fixture(comms, name, mode):
     from nano_vllm_learn_b200 import ops
     c = cases.make_rowparallel_case(name)
@@ -139,7 +139,7 @@ def test_back_to_back_calls_alternate_buffers(comms):
         w = (torch.randn(h, k, generator=g) * k ** -0.5).to(torch.bfloat16)
         xs, ws = rpo.shard_inputs(x, w, 2)
         plans.append((xs, ws, [t.to(f"cuda:{r}") for r, t in enumerate(xs)], [t.to(f"cuda:{r}") for r, t in enumerate(ws)],
-                      i % 2))
+                      [0, 1, 3][i % 3]))
     results = []
     for xs, ws, xd, wd, mode in plans:
         ops.rowparallel_set_plan(0, 0, mode)
