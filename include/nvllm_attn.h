@@ -340,9 +340,15 @@ NVLLM_API int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride,
                                        void* const* comm_ptrs, size_t comm_bytes,
                                        int32_t rank, int32_t world, void* stream);
 /* The launch plan is a function of the shape alone, so every rank agrees:
- * feature tile (32|64 output features per CTA), k split, exchange mode
- * (0 = one-shot: partials pushed to every rank, each rank reduces everything;
- *  1 = two-shot: partials pushed to the tile's owner, owner broadcasts bf16). */
+ * feature tile (32|64 output features per CTA), k split (= thread-block
+ * cluster size; the launcher may halve it to fit the device's co-resident
+ * cluster capacity), exchange mode
+ * (3 = one-shot with flag-in-data words {payload, call epoch}: partials
+ *      pushed to every rank, no fence or separate flag; pushes <= 1 MiB;
+ *  0 = one-shot with release/acquire flags; pushes <= 4 MiB;
+ *  1 = two-shot: partials pushed to the tile's owner, owner broadcasts bf16;
+ *  2 = profiling only, never planned: the rank's own partial goes straight
+ *      to y, nothing is exchanged). */
 NVLLM_API int nvllm_rowparallel_plan(int32_t n_tokens, int32_t in_features_per_rank,
                            int32_t out_features, int32_t world,
                            int32_t* feature_tile_out, int32_t* ksplit_out,

@@ -7,7 +7,7 @@ straight into the peers' inboxes and reduce what arrives, so one launch replaces
 
 `TPComm` owns the peer-mapped buffers: one cudaMalloc per rank, exchanged between the rank PROCESSES (the reference
 spawns one process per GPU, llm_engine.py:29-36) as CUDA IPC handles through the existing process group.  Batches
-above `ENGINE_MAX_TOKENS` (prefill: GEMM-bound, the collective is bandwidth- not latency-bound) keep the reference's
+above `engine_max_tokens()` (prefill: GEMM-bound, the collective is bandwidth- not latency-bound) keep the reference's
 own F.linear + dist.all_reduce.  No CPU path: CUDA tensors and the built library are required.
 """
 from __future__ import annotations
@@ -20,10 +20,20 @@ import torch
 from . import _lib, ops
 
 MAX_TOKENS = 512          # nvllm_rowparallel_linear_allreduce's n_tokens limit (include/nvllm_attn.h (6))
-# Batches the engine hands to the fused kernel.  Measured on 2 and 4 B200s (profiles/r01_rowparallel_tp{2,4}_v3_*.jsonl):
-# 1.3-1.9x cuBLAS + NCCL up to 64 tokens on every shard shape, about parity at 128-256 on Qwen3-0.6B shards and slower
-# on 8B-shape shards, slower at 512 — so larger batches keep the reference's own forward.
-ENGINE_MAX_TOKENS = int(os.environ.get("NVLLM_FUSED_ALLREDUCE_MAX_TOKENS", "64"))
+# Batches the engine hands to the fused kernel, by weight-shard size.  Measured on 2 and 4 B200s against cuBLAS + NCCL
+# (profiles/r01_rowparallel_tp2_v4_flag_in_data.jsonl, r01_rowparallel_tp4_v3_static_tiles.jsonl): Qwen3-0.6B shards
+# (2-3 MiB) 2.1-2.5x up to 64 tokens and 1.3-1.4x up to 256; 8B-shape o_proj (16 MiB) 1.1-2.1x up to 64; 8B-shape
+# down_proj (50 MiB) 1.2-2.0x up to 32 and slower from 64 on.  Larger batches keep the reference's own forward.
+_ENV_MAX = os.environ.get("NVLLM_FUSED_ALLREDUCE_MAX_TOKENS")
+
+
+def engine_max_tokens(in_features_per_rank: int, out_features: int) -> int:
+    if _ENV_MAX is not None:
+        return min(MAX_TOKENS, int(_ENV_MAX))
+    wbytes = in_features_per_rank * out_features * 2
+    return 256 if wbytes <= (4 << 20) else 64 if wbytes <= (16 << 20) else 32
+
+
 _IPC_HANDLE_BYTES = 64
 
 
@@ -194,9 +204,10 @@ def install(RowParallelLinear) -> None:
                                  supported(self.input_size_per_partition, self.output_size, self.tp_size))
         if self._nvllm_fused:
             _SHAPES.add((self.input_size_per_partition, self.output_size))
+        self._nvllm_fused_max = engine_max_tokens(self.input_size_per_partition, self.output_size)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > min(MAX_TOKENS, ENGINE_MAX_TOKENS) or \
+        if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > self._nvllm_fused_max or \
                 x.dtype != torch.bfloat16 or not x.is_cuda:
             return ref_forward(self, x)
         return ops.rowparallel_linear_allreduce(x, self.weight, self.bias, get_comm())
