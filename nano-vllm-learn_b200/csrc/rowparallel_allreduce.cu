@@ -126,7 +126,13 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int STAGES = rp_stages(BH, MT, BK);
   constexpr int NT = MT * 16;             // staged token rows (rows past the last token are zero-filled)
-  constexpr int NJ = BH / 32;             // 8-feature n-tiles per warp (4 warps split the BH features)
+  // warp grid: 4 warps split the BH features (decode tiles), or 2 x 2 over (token tiles, features) for 64-feature
+  // tiles with >= 32 tokens -- each A fragment then feeds 4 MMAs and each B fragment MT/2, which halves the
+  // shared-memory reads per MMA
+  constexpr int WM = (BH == 64 && MT >= 2) ? 2 : 1, WN = 4 / WM;
+  constexpr int MW = MT / WM;             // 16-token m-tiles per warp
+  constexpr int FW = BH / WN;             // features per warp
+  constexpr int NJ = FW / 8;              // 8-feature n-tiles per warp
   constexpr int F4 = BH / 4;              // float4 chunks per tile row
   constexpr int EP_STRIDE = BH + 8;       // floats per staged epilogue row (padding breaks bank conflicts)
   constexpr size_t TILE_BYTES = size_t(RP_TOKB) * BH * 4;   // inbox footprint of one (slot, tile)
@@ -173,19 +179,20 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     }
   };
 
-  float acc[MT][NJ][4];
+  const int wm = warp / WN, wn = warp % WN;
+  float acc[MW][NJ][4];
 #pragma unroll
-  for (int m = 0; m < MT; ++m)
+  for (int m = 0; m < MW; ++m)
 #pragma unroll
     for (int j = 0; j < NJ; ++j)
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
 
   // ldmatrix lane addresses inside a stage (the k16 step only flips chunk bits: XOR with a constant)
-  const int brow = warp * (BH / 4) + (lane & 7);
+  const int brow = wn * FW + (lane & 7);
   const uint32_t boff = brow * ROWB, bsw = ((lane >> 3) ^ (brow & 7)) << 4;          // chunk kk2*4 + (lane>>3)
   const int arow = lane & 15;
-  const uint32_t aoff = W_STAGE + arow * ROWB, asw = ((lane >> 4) ^ (arow & 7)) << 4;  // chunk kk*2 + (lane>>4)
+  const uint32_t aoff = W_STAGE + (wm * MW * 16 + arow) * ROWB, asw = ((lane >> 4) ^ (arow & 7)) << 4;  // chunk kk*2 + (lane>>4)
 
 #pragma unroll
   for (int s = 0; s < STAGES - 1; ++s) {
@@ -208,7 +215,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       for (int kh = 0; kh < 2; ++kh) {
         const int kk = kk2 * 2 + kh;
 #pragma unroll
-        for (int m = 0; m < MT; ++m) {
+        for (int m = 0; m < MW; ++m) {
           uint32_t a0, a1, a2, a3;
           ldmatrix_x4(a0, a1, a2, a3, sb + aoff + m * (16 * ROWB) + (asw ^ ((kk * 2) << 4)));
 #pragma unroll
@@ -224,12 +231,12 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-    for (int m = 0; m < MT; ++m) {
+    for (int m = 0; m < MW; ++m) {
 #pragma unroll
       for (int j = 0; j < NJ; ++j) {
-        const int col = warp * (BH / 4) + j * 8 + 2 * t;
-        *reinterpret_cast<float2*>(ep + (m * 16 + g) * EP_STRIDE + col) = make_float2(acc[m][j][0], acc[m][j][1]);
-        *reinterpret_cast<float2*>(ep + (m * 16 + g + 8) * EP_STRIDE + col) = make_float2(acc[m][j][2], acc[m][j][3]);
+        const int col = wn * FW + j * 8 + 2 * t, row = (wm * MW + m) * 16 + g;
+        *reinterpret_cast<float2*>(ep + row * EP_STRIDE + col) = make_float2(acc[m][j][0], acc[m][j][1]);
+        *reinterpret_cast<float2*>(ep + (row + 8) * EP_STRIDE + col) = make_float2(acc[m][j][2], acc[m][j][3]);
       }
     }
   }
@@ -529,16 +536,23 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   if (k_per_rank <= 0 || k_per_rank % RP_BK_MIN || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
   const int tok_blocks = (n_tokens + RP_TOKB - 1) / RP_TOKB;
   const int cap = RP_PLAN_CAP;
-  // 64-feature tiles once the x tile (re-read by every feature tile) outweighs the W tile
-  int bh = (n_tokens <= 64 && (out_features / 32) * tok_blocks <= cap) ? 32 : 64;
+  // 64-feature tiles (2 x 2 warp grid, half the x re-reads) above 32 tokens when they still give >= 128 CTAs, and
+  // always above 64 tokens or when 32-feature tiles would not fit one wave
+  auto ksplit_for = [&](int tiles) {
+    int ks = 1;
+    for (int c = 2; c <= RP_MAX_KSPLIT; c *= 2) {
+      if (k_per_rank % (c * RP_BK_MIN) || k_per_rank / c < 256 || tiles * c > cap) break;
+      ks = c;
+    }
+    return ks;
+  };
+  const int tiles64 = (out_features / 64) * tok_blocks;
+  const bool wide = n_tokens > 64 || (n_tokens > 32 && tiles64 * ksplit_for(tiles64) >= 128);
+  int bh = (!wide && (out_features / 32) * tok_blocks <= cap) ? 32 : 64;
   if (g_force_bh == 32 || g_force_bh == 64) bh = g_force_bh;
   const int h_tiles = out_features / bh, n_tiles = h_tiles * tok_blocks;
   if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
-  int ksplit = 1;
-  for (int c = 2; c <= RP_MAX_KSPLIT; c *= 2) {
-    if (k_per_rank % (c * RP_BK_MIN) || k_per_rank / c < 256 || n_tiles * c > cap) break;
-    ksplit = c;
-  }
+  int ksplit = ksplit_for(n_tiles);
   if (g_force_ksplit > 0) {
     ksplit = g_force_ksplit;
     if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK_MIN) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;

@@ -87,7 +87,7 @@ def main():
         ws = [(torch.randn(h, k, generator=g) * k ** -0.5).to(torch.bfloat16).to(dev) for _ in range(min(ncopies, 4))]
         while len(ws) < ncopies:          # distinct memory, repeated values
             ws.append(ws[len(ws) % 4].clone())
-        for n in (1, 16, 64, 128):
+        for n in (1, 16, 32, 64, 128, 256):
             x = torch.randn(n, k, generator=g).to(torch.bfloat16).to(dev)
             y = torch.empty(n, h, dtype=torch.bfloat16, device=dev)
             got = ops.rowparallel_linear_allreduce(x, ws[0], None, comm).float()

@@ -1,10 +1,13 @@
 #!/bin/bash
 # 1-GPU tuning run for the GEMM part of the fused RowParallelLinear kernel (exchange off).  Every step is bounded.
 mkdir -p gpurun_out
-timeout 150 python tools/bench_rowparallel_local.py --out gpurun_out/rowparallel_local_bk128.jsonl > gpurun_out/rp_local_bk128.log 2>&1
-echo "bk auto rc=$?"; tail -22 gpurun_out/rp_local_bk128.log | cut -c1-420
-NVLLM_RP_BK=64 timeout 150 python tools/bench_rowparallel_local.py --out gpurun_out/rowparallel_local_bk64.jsonl > gpurun_out/rp_local_bk64.log 2>&1
-echo "bk64 rc=$?"; tail -22 gpurun_out/rp_local_bk64.log | cut -c1-420
-timeout 150 ncu --set full --clock-control none --import-source on -k regex:rowparallel -s 3 -c 1 -f -o gpurun_out/rp_local_gemm \
+timeout 100 python tools/bench_rowparallel_local.py --iters 4 --out gpurun_out/rowparallel_local.jsonl > gpurun_out/rp_local.log 2>&1
+echo "local rc=$?"; python - <<'PY'
+import json
+for l in open('gpurun_out/rowparallel_local.jsonl'):
+    r = json.loads(l)
+    print(r['shape'], r['n'], r['plan'], 'diff', r['max_abs_diff_vs_cublas'], 'fused', r['us_fused_hbm'], 'cublas', r['us_cublas_hbm'], 'GB/s', r['w_gbs_fused_hbm'])
+PY
+timeout 60 ncu --set full --clock-control none --import-source on -k regex:rowparallel -s 3 -c 1 -f -o gpurun_out/rp_local_gemm_v5 \
     python tools/bench_rowparallel_local.py --ncu > gpurun_out/rp_local_ncu.log 2>&1
-echo "ncu rc=$?"; tail -3 gpurun_out/rp_local_ncu.log
+echo "ncu rc=$?"; tail -2 gpurun_out/rp_local_ncu.log
