@@ -18,10 +18,17 @@
 //      order in fp32 (bit-identical on every rank), adds the bias, rounds to bf16 once and writes y (mode 0), or
 //      writes the reduced bf16 slice into every rank's result area, publishes a second flag, and every rank copies
 //      its slice into y (mode 1).
+//   Decode-sized pushes (<= 1 MiB per rank) use mode 3 instead of 0: the slice travels as 8-byte {payload, call
+//   epoch} words (two per 16-byte volatile store, the NCCL "LL" layout) and the receiving thread polls the words of
+//   its own elements until every epoch matches -- no fence, no separate flag, no CTA barrier on either side.  These
+//   words live in a region of their own, zeroed at allocation, so nothing but an older epoch can ever sit there.
 // Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
 // epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
 // waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
-// within one co-resident wave.
+// within one co-resident wave of clusters.
+// Why two parities suffice: a rank finishes call e only after it has received, for every tile it reduces, what each
+// peer pushed in call e -- so every peer has STARTED call e and therefore (stream order) finished call e-1.  A rank
+// that is already pushing call e+1 (same parity as e-1) can thus only meet peers that are done reading e-1.
 #include <cooperative_groups.h>
 
 #include <cstdlib>

@@ -144,16 +144,25 @@ class TPComm:
 _COMM: TPComm | None = None
 _SHAPES: set[tuple[int, int]] = set()
 _ENABLED = False
-# NVLLM_FUSED_ALLREDUCE: "1" fused kernel, "0" the reference's F.linear + NCCL all_reduce.
-DEFAULT_ENV = "0"
+# NVLLM_FUSED_ALLREDUCE: "1" fused kernel, "0" the reference's F.linear + NCCL all_reduce.  Unset: fused at the world
+# sizes it has been validated and measured at on B200s (2 and 4: tests/test_gpu_rowparallel.py, profiles/
+# r01_rowparallel_tp{2,4}_*.jsonl), the reference's collective elsewhere (8 GPUs: opt in with "1").
+VALIDATED_WORLDS = (2, 4)
 
 
 def configure(cuda_backend: bool) -> None:
-    """Called by ModelRunner.__init__ (INTEGRATION.md edit A7) before the model is built: the fused op is part of
-    the `cuda` backend only, so the reference's other backends keep their stock collective.  Also drops the
-    communicator of a previous engine in this process (its peers are gone)."""
+    """Called by ModelRunner.__init__ (INTEGRATION.md edit A7) after the process group exists and before the model
+    is built: the fused op is part of the `cuda` backend only, so the reference's other backends keep their stock
+    collective.  Also drops the communicator of a previous engine in this process (its peers are gone)."""
     global _ENABLED
-    _ENABLED = bool(cuda_backend) and os.environ.get("NVLLM_FUSED_ALLREDUCE", DEFAULT_ENV) != "0"
+    env = os.environ.get("NVLLM_FUSED_ALLREDUCE")
+    if env is None:
+        import torch.distributed as dist
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        want = world in VALIDATED_WORLDS
+    else:
+        want = env != "0"
+    _ENABLED = bool(cuda_backend) and want
     release()
 
 

@@ -117,6 +117,19 @@ def _patch_worker(rank, world, port, q):
         ok = ok0 and m._nvllm_fused and (c["k"] // world, c["h"]) in rowparallel_cuda._SHAPES
         odd = mod.RowParallelLinear(200, 100)          # shape the kernel does not take: stays on the reference path
         ok = ok and not odd._nvllm_fused
+        # the engine hands over batches by shard size (measured crossover vs cuBLAS + NCCL): 3 MiB shard -> 256 tokens
+        ok = ok and m._nvllm_fused_max == 256 and rowparallel_cuda.engine_max_tokens(2048, 4096) == 64 \
+            and rowparallel_cuda.engine_max_tokens(6144, 4096) == 32
+        # env unset: on at the validated world sizes (2 is one); "0": the reference's collective
+        del os.environ["NVLLM_FUSED_ALLREDUCE"]
+        rowparallel_cuda.configure(True)
+        ok = ok and rowparallel_cuda.enabled() and world in rowparallel_cuda.VALIDATED_WORLDS
+        os.environ["NVLLM_FUSED_ALLREDUCE"] = "0"
+        rowparallel_cuda.configure(True)
+        ok = ok and not rowparallel_cuda.enabled() and not mod.RowParallelLinear(1024, 1024)._nvllm_fused
+        os.environ["NVLLM_FUSED_ALLREDUCE"] = "1"
+        rowparallel_cuda.configure(True)
+        rowparallel_cuda._SHAPES.add((c["k"] // world, c["h"]))
         # CPU tensors never reach the CUDA op: the patched forward must be the reference's own
         with torch.no_grad():
             y = m(c["x"].chunk(world, dim=1)[rank].contiguous())
