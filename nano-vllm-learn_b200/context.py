@@ -47,7 +47,6 @@ def set_context(is_prefill, cu_seqlens_q=None, cu_seqlens_k=None, max_seqlen_q=0
 
 
 def reset_context() -> None:
+    """Back to the all-defaults record, like the reference (`utils/context.py:25-27`)."""
     global _ACTIVE
-    # One record per process: each tensor-parallel rank is its own spawned process (llm_engine.py:29-36) and runs
-# a single Python thread, so a module-level slot is all the engine needs.
-_ACTIVE = Context()
+    _ACTIVE = Context()
