@@ -190,10 +190,20 @@ NVLLM_API int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_strid
  * -1 = default (tcgen05). */
 NVLLM_API int nvllm_varlen_prefill_set_variant(int32_t variant);
 
-/* Debug hook: when non-NULL, CTA (q-tile 0, head 0, sequence 0) of the tcgen05
- * kernel dumps its first raw S tile (128x128 fp32) followed by its first raw
- * O partial (128x128 fp32) to this device buffer (>= 131072 bytes). */
-NVLLM_API void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr);
+/* Which kernel served the most recent nvllm_varlen_prefill call of this process:
+ * 1 = tcgen05/TMEM tile kernel, 0 = mma.sync tile kernel, -1 = none launched yet.
+ * The tcgen05 kernel needs TMA bounds (total_q, total_k > 0), the driver's
+ * tensor-map encoder and, for paged K/V, block_size % 128 == 0; everything else
+ * runs the mma.sync kernel.  nvllm_varlen_prefill_path_count(path) counts the
+ * launches per path since load, so a caller can assert what actually ran. */
+NVLLM_API int32_t nvllm_varlen_prefill_last_path(void);
+NVLLM_API int64_t nvllm_varlen_prefill_path_count(int32_t path);
+
+/* The tcgen05 kernel bounds every mbarrier wait (2 s): on a timeout it latches
+ * an error word and drains instead of trapping.  Returns (and clears) that word
+ * for the current device in *code_out; 0 = no error.  Synchronises the device:
+ * call it outside graph capture (tests, end of a benchmark, engine shutdown). */
+NVLLM_API int nvllm_varlen_prefill_error(uint32_t* code_out);
 
 /* ------------------------------------------------------------------------
  * (3b) fused pre-attention step (SURVEY §8f "next", rank 1): per-head q/k
@@ -317,11 +327,22 @@ NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
  *   nothing and need no host synchronisation between ranks: a call epoch in
  *   the buffer's control area advances on the device.  A peer that never
  *   arrives makes the kernel give up after the configured timeout (default
- *   20 s) and latch an error word readable with nvllm_tp_comm_status.
+ *   20 s; nvllm_rowparallel_set_plan) and latch an error word: on the device
+ *   (nvllm_tp_comm_status, synchronous) and in mapped host memory
+ *   (nvllm_rowparallel_poll_error, free to poll).
  * ---------------------------------------------------------------------- */
 NVLLM_API size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens,
                                     int32_t in_features_per_rank,
                                     int32_t out_features);
+/* The parts nvllm_rowparallel_comm_bytes adds up: header (control words + flags), and per epoch parity the
+ * "regular" area (fp32 inboxes + two-shot result area, growing from the start of the parity) and the
+ * flag-in-data inbox (anchored at its end).  comm_bytes = header + 2 * (regular + flag_in_data).  A buffer shared
+ * by several shapes must hold header + 2 * (max regular + max flag_in_data) over those shapes, so that no
+ * call's fp32/bf16 data can land in words another call polls as {payload, epoch}. */
+NVLLM_API int nvllm_rowparallel_comm_layout(int32_t world, int32_t max_tokens,
+                                  int32_t in_features_per_rank, int32_t out_features,
+                                  size_t* header_bytes_out, size_t* regular_bytes_out,
+                                  size_t* flag_in_data_bytes_out);
 NVLLM_API int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out /* 64 bytes or NULL */);
 NVLLM_API int nvllm_tp_comm_open(const void* ipc_handle, void** peer_ptr);
 NVLLM_API int nvllm_tp_comm_close(void* peer_ptr);
@@ -331,6 +352,10 @@ NVLLM_API int nvllm_tp_comm_reset(void* dev_ptr, void* stream);
 NVLLM_API int nvllm_tp_comm_enable_peer(int32_t peer_device);
 /* synchronous read-back of the call epoch and the latched error word (0 = none) */
 NVLLM_API int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* error_out);
+/* Non-blocking: the timeout latch as a mapped pinned HOST word (0 = none, else 1 + the tile whose peer never
+ * arrived in some launch of this process); plain memory read, no CUDA call, usable after every launch or graph
+ * replay.  clear != 0 resets it.  The results of a call that timed out are undefined. */
+NVLLM_API int nvllm_rowparallel_poll_error(uint32_t* error_out, int32_t clear);
 NVLLM_API int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride,
                                        const void* x, int64_t x_row_stride,
                                        const void* weight, int64_t w_row_stride,
@@ -357,11 +382,8 @@ NVLLM_API int nvllm_rowparallel_plan(int32_t n_tokens, int32_t in_features_per_r
 NVLLM_API int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit,
                                int32_t mode, int64_t timeout_ms);
 
-/* Measurement aid (tools/membench.py), not on the product path: streams `bytes`
- * of `buf` with contiguous warp reads (pattern 0) or with the decode kernel's
- * 256-byte-row / token-stride access shape (pattern 1, hkv heads). */
-NVLLM_API int nvllm_debug_stream_read(const void* buf, int64_t bytes, int32_t pattern,
-                            int32_t hkv, int32_t blocks, void* sink, void* stream);
+/* Measurement and debug aids (read-bandwidth probe, prefill trace buffer) are not
+ * part of this ABI: include/nvllm_tools.h, built into lib/libnvllm_tools.so. */
 
 #ifdef __cplusplus
 }

@@ -31,7 +31,9 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p,
                                      c_int64, c_int32, c_int32, c_int32, c_int32, c_float, c_void_p]),
     "nvllm_varlen_prefill_set_variant": (c_int, [c_int32]),
-    "nvllm_varlen_prefill_set_debug_buffer": (None, [c_void_p]),
+    "nvllm_varlen_prefill_last_path": (c_int32, []),
+    "nvllm_varlen_prefill_path_count": (c_int64, [c_int32]),
+    "nvllm_varlen_prefill_error": (c_int, [ctypes.POINTER(ctypes.c_uint32)]),
     "nvllm_qk_norm_rope_store": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                          c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
                                          c_int32, c_int32, c_void_p]),
@@ -39,6 +41,9 @@ SIGNATURES = {
                                     c_uint64, c_uint64, c_void_p, c_size_t, c_void_p]),
     "nvllm_sample_workspace_bytes": (c_size_t, [c_int32]),
     "nvllm_rowparallel_comm_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
+    "nvllm_rowparallel_comm_layout": (c_int, [c_int32, c_int32, c_int32, c_int32, ctypes.POINTER(c_size_t),
+                                              ctypes.POINTER(c_size_t), ctypes.POINTER(c_size_t)]),
+    "nvllm_rowparallel_poll_error": (c_int, [ctypes.POINTER(ctypes.c_uint32), c_int32]),
     "nvllm_tp_comm_alloc": (c_int, [c_size_t, ctypes.POINTER(c_void_p), c_void_p]),
     "nvllm_tp_comm_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
     "nvllm_tp_comm_close": (c_int, [c_void_p]),
@@ -51,9 +56,14 @@ SIGNATURES = {
                                                    c_int32, c_int32, c_void_p]),
     "nvllm_rowparallel_plan": (c_int, [c_int32, c_int32, c_int32, c_int32, _P32, _P32, _P32]),
     "nvllm_rowparallel_set_plan": (c_int, [c_int32, c_int32, c_int32, c_int64]),
-    "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),
+}
+
+# include/nvllm_tools.h (lib/libnvllm_tools.so only; tools/*.py call load_tools())
+TOOLS_SIGNATURES = {
+    "nvllm_varlen_prefill_set_debug_buffer": (None, [c_void_p]),
+    "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
 }
 
 ABI_VERSION = 1
@@ -83,6 +93,24 @@ def load() -> ctypes.CDLL:
     if got != ABI_VERSION:
         raise NvllmError(f"ABI mismatch: library reports {got}, binding expects {ABI_VERSION}")
     _LIB = lib
+    return lib
+
+
+def load_tools() -> ctypes.CDLL:
+    """Measurement/debug build (build.py --tools): becomes THE library of this process, so ops.* run the traced
+    kernels.  Must be called before anything else loaded the product library."""
+    global _LIB
+    path = _PKG / "lib" / "libnvllm_tools.so"
+    if not path.exists():
+        raise NvllmError(f"{path} not found: build it with `python nano-vllm-learn_b200/build.py --tools`")
+    if _LIB is not None and not hasattr(_LIB, "nvllm_debug_stream_read"):
+        raise NvllmError("the product library is already loaded; call load_tools() first")
+    os.environ["NVLLM_ATTN_LIB"] = str(path)
+    lib = load()
+    for name, (restype, argtypes) in TOOLS_SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
     return lib
 
 

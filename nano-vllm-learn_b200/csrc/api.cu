@@ -17,6 +17,16 @@ int record_cuda_error(cudaError_t e) {
   return NVLLM_ERR_CUDA;
 }
 
+int device_sm_count() {
+  static int cache[kMaxDevices] = {};
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev >= 0 && dev < kMaxDevices && cache[dev] > 0) return cache[dev];
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+  if (dev >= 0 && dev < kMaxDevices) cache[dev] = v;
+  return v;
+}
+
 }  // namespace nvllm
 
 extern "C" {

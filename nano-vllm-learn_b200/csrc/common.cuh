@@ -20,6 +20,26 @@ int record_cuda_error(cudaError_t e);  // returns NVLLM_ERR_CUDA (or OK)
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// ---- per-device host state ---------------------------------------------------
+// One process may drive several GPUs (TPComm.single_process, the rowparallel tests), and both the SM count and
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) are per device: nothing below is cached per process.
+constexpr int kMaxDevices = 64;
+int device_sm_count();                 // SM count of the CURRENT device (cached per device; 148 if the query fails)
+struct PerDeviceOnce {
+  bool done[kMaxDevices] = {};
+};
+// Runs `configure()` the first time it is called on each device; devices >= kMaxDevices configure every time.
+template <class F>
+inline cudaError_t once_per_device(PerDeviceOnce& state, F configure) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < kMaxDevices && state.done[dev]) return cudaSuccess;
+  e = configure();
+  if (e == cudaSuccess && dev >= 0 && dev < kMaxDevices) state.done[dev] = true;
+  return e;
+}
+
 // ---- small PTX wrappers -----------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

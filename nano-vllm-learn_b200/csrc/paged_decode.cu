@@ -322,27 +322,15 @@ constexpr int kNumVariants = 8;
 // (two 4-warp CTAs per SM).  Same warps and bytes in flight per SM; measured in profiles/r01_decode_sweep_*.
 static int g_variant = -1;
 
-static int sm_count_cached() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
-      v = 148;
-    n = v;
-  }
-  return n;
-}
+static int sm_count_cached() { return device_sm_count(); }
 
 template <class Cfg>
 static cudaError_t launch_decode(const DecodeParams& p, int bs, int hkv, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg::kSmemBytes);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+  static PerDeviceOnce configured;
+  cudaError_t e0 = once_per_device(configured, [] {
+    return cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  if (e0 != cudaSuccess) return e0;
   dim3 grid(p.num_splits, hkv, bs);
   paged_decode_kernel<Cfg><<<grid, Cfg::kWarps * 32, Cfg::kSmemBytes, stream>>>(p);
   return cudaGetLastError();

@@ -31,4 +31,7 @@ struct PrefillParams {
 int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, int max_seqlen_k,
                            cudaStream_t stream, bool* handled);
 
+// returns (and clears) the tcgen05 kernel's mbarrier-timeout latch on the current device; synchronises
+int prefill_tcgen05_error_fetch(unsigned int* code);
+
 }  // namespace nvllm

@@ -20,6 +20,9 @@
 // warpgroup does its softmax (ping-pong).  TMEM: S_A S_B O_A O_B = 4 x 128 columns = all 512.
 #include "prefill_params.cuh"
 #include "tcgen05.cuh"
+#ifdef NVLLM_TOOLS_BUILD
+#include "../../include/nvllm_tools.h"
+#endif
 
 namespace nvllm {
 
@@ -341,7 +344,9 @@ bool make_map(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, 
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+#ifdef NVLLM_TOOLS_BUILD
 float* g_debug = nullptr;
+#endif
 
 }  // namespace
 
@@ -355,38 +360,39 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
   if (!make_map(&tq, p.q, static_cast<uint64_t>(p.num_q_heads) * kHeadDim, p.total_q, p.q_row_stride)) return NVLLM_OK;
   if (!make_map(&tk, p.k, kv_cols, p.total_k, p.k_row_stride)) return NVLLM_OK;
   if (!make_map(&tv, p.v, kv_cols, p.total_k, p.v_row_stride)) return NVLLM_OK;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce configured;
+  cudaError_t e0 = once_per_device(configured, [] {
     cudaError_t e = cudaFuncSetAttribute(prefill_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kSmemBytes);
+#ifdef NVLLM_TOOLS_BUILD
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(prefill_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (e != cudaSuccess) return record_cuda_error(e);
-    configured = true;
-  }
+#endif
+    return e;
+  });
+  if (e0 != cudaSuccess) return record_cuda_error(e0);
   const int num_pairs = (max_seqlen_q + 2 * TM - 1) / (2 * TM);
   const int64_t total = static_cast<int64_t>(num_pairs) * p.num_q_heads * batch;
   if (total > INT32_MAX) return NVLLM_ERR_UNSUPPORTED;
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
-      v = 148;
-    sms = v;
-  }
+  const int sms = device_sm_count();
   const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);   // persistent: one CTA per SM
+#ifdef NVLLM_TOOLS_BUILD
   if (g_debug)
     prefill_tcgen05_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, g_debug);
   else
+#endif
     prefill_tcgen05_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, nullptr);
   note_launch();
   *handled = true;
   return record_cuda_error(cudaGetLastError());
 }
 
+int prefill_tcgen05_error_fetch(unsigned int* code) { return record_cuda_error(tc::tc_error_fetch(code)); }
+
 }  // namespace nvllm
 
+#ifdef NVLLM_TOOLS_BUILD
 extern "C" void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr) {
   nvllm::g_debug = static_cast<float*>(device_ptr);
 }
+#endif

@@ -20,8 +20,14 @@
 //      its slice into y (mode 1).
 //   Decode-sized pushes (<= 1 MiB per rank) use mode 3 instead of 0: the slice travels as 8-byte {payload, call
 //   epoch} words (two per 16-byte volatile store, the NCCL "LL" layout) and the receiving thread polls the words of
-//   its own elements until every epoch matches -- no fence, no separate flag, no CTA barrier on either side.  These
-//   words live in a region of their own, zeroed at allocation, so nothing but an older epoch can ever sit there.
+//   its own elements until every epoch matches -- no fence, no separate flag, no CTA barrier on either side.
+//   Hardware assumption, the one NCCL's LL protocol makes with the very same instructions (its storeLL / readLL are
+//   st/ld.volatile.global.v4.u32 over {data1, flag1, data2, flag2}): each naturally aligned 8-byte half of a 16-byte
+//   vector access is single-copy atomic over NVLink and in L2, so a half whose epoch matches carries that epoch's
+//   payload.  tests/test_gpu_rowparallel.py::test_ll_exchange_stress hammers it with randomised payloads.
+//   These words live in a region of their own -- anchored at the END of each parity, while the fp32 inboxes and the
+//   two-shot result area of every other plan grow from its start, and nvllm_rowparallel_comm_layout sizes the buffer
+//   so the two never meet -- zeroed at allocation, so nothing but an older epoch can ever sit there.
 // Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
 // epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
 // waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
@@ -72,6 +78,7 @@ struct RpParams {
   unsigned long long res_off;     // offset of the result area inside a parity (mode 1)
   unsigned long long ll_off;      // offset of the flag-in-data inbox inside a parity (mode 3)
   unsigned long long timeout_ns;
+  uint32_t* host_err;             // mapped pinned host word: a timeout is visible to the host without a sync
 };
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
@@ -104,14 +111,22 @@ __device__ __forceinline__ uint4 ld_volatile_v4u(const void* p) {
 }
 
 // Spin until *flag has reached `epoch` (wrap-safe); on timeout record the tile and give up.
+__device__ __forceinline__ void latch_timeout(RpControl* ctrl, uint32_t* host_err, int tile) {
+  atomicCAS(&ctrl->error, 0u, 1u + static_cast<uint32_t>(tile));
+  if (host_err) {
+    *reinterpret_cast<volatile uint32_t*>(host_err) = 1u + static_cast<uint32_t>(tile);
+    __threadfence_system();
+  }
+}
+
 __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, RpControl* ctrl, int tile,
-                                          unsigned long long timeout_ns) {
+                                          unsigned long long timeout_ns, uint32_t* host_err) {
   if (static_cast<int32_t>(ld_acquire_sys(flag) - epoch) >= 0) return;
   const unsigned long long t0 = globaltimer_ns();
   while (static_cast<int32_t>(ld_acquire_sys(flag) - epoch) < 0) {
     __nanosleep(32);
     if (globaltimer_ns() - t0 > timeout_ns) {
-      atomicCAS(&ctrl->error, 0u, 1u + static_cast<uint32_t>(tile));
+      latch_timeout(ctrl, host_err, tile);
       return;
     }
   }
@@ -320,7 +335,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     if (tid < p.world)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES +
                                                   (static_cast<size_t>(tid * p.ksplit + ks) * RP_MAX_TILES + tile) * 4),
-                epoch, ctrl, tile, p.timeout_ns);
+                epoch, ctrl, tile, p.timeout_ns, p.host_err);
     __syncthreads();
     const uint8_t* const in0 = local + par_off + static_cast<size_t>(tile) * TILE_BYTES;
     const size_t slot_stride = static_cast<size_t>(p.n_tiles) * TILE_BYTES;
@@ -373,7 +388,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
           const unsigned long long now = globaltimer_ns();
           if (t0 == 0) t0 = now;
           if (now - t0 > p.timeout_ns) {
-            atomicCAS(&ctrl->error, 0u, 1u + static_cast<uint32_t>(tile));
+            latch_timeout(ctrl, p.host_err, tile);
             break;
           }
         }
@@ -399,7 +414,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     if (tid == 0)
       wait_flag(reinterpret_cast<const uint32_t*>(local + RP_HDR_BYTES + RP_FLAG1_BYTES +
                                                   (static_cast<size_t>(ks) * RP_MAX_TILES + tile) * 4),
-                epoch, ctrl, tile, p.timeout_ns);
+                epoch, ctrl, tile, p.timeout_ns, p.host_err);
     __syncthreads();
     const uint8_t* const res = local + par_off + p.res_off + static_cast<size_t>(tile) * RES_TILE_BYTES;
     for (int i = r_lo * F4 + tid; i < r_hi * F4; i += RP_THREADS) {
@@ -424,13 +439,34 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 // ---- host side ---------------------------------------------------------------------------------------------
 struct RpPlan {
   int bh, ksplit, mode, h_tiles, tok_blocks, n_tiles, kc, mt, bk;
-  size_t smem, par_need, res_off, ll_off;
+  size_t smem, res_off;
+  size_t reg_need;   // bytes this plan uses at the START of a parity (fp32 inboxes + two-shot result area); 0 in mode 3
+  size_t ll_need;    // bytes this plan uses at the END of a parity (flag-in-data inbox); 0 unless mode 3
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
 std::unordered_map<void*, size_t> g_comm_bytes;   // buffers from nvllm_tp_comm_alloc (reset clears them whole)
 int g_force_bk = -1;   // tuning only: NVLLM_RP_BK=64|128 (read once)
 unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
+
+// One mapped, pinned host word per process: a kernel whose peer never arrived writes 1 + tile into it besides the
+// device-side latch, so the host notices at its next poll (nvllm_rowparallel_poll_error: a plain memory read, no
+// CUDA call, no synchronisation -- usable after every launch or graph replay).  nullptr if pinned memory is refused.
+uint32_t* rp_host_error_word() {
+  static uint32_t* word = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      memset(p, 0, 64);
+      word = static_cast<uint32_t*>(p);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return word;
+}
 
 int rp_nt16(int n_tokens) { return n_tokens >= RP_TOKB ? RP_TOKB : ((n_tokens + 15) & ~15); }
 
@@ -578,11 +614,14 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   pl->bk = bk;
   pl->mt = mt;
   pl->smem = rp_smem_bytes(bh, mt, bk);
-  // one parity: [fp32 inbox, one slot per rank | bf16 result area (mode 1) | flag-in-data inbox (mode 3)]; the
-  // mode-3 area never holds anything but {payload, epoch} words, so a stale word cannot pass for a current one
+  // one parity: [fp32 inbox, one slot per rank | bf16 result area (mode 1) | ... free ... | flag-in-data inbox
+  // (mode 3)].  The mode-3 inbox is anchored at the END of the parity whatever the plan, and the buffer is sized
+  // (nvllm_rowparallel_comm_layout) as max(regular) + max(flag-in-data) over every plan, so no fp32 partial or bf16
+  // result of ANY call can land in a word a mode-3 call reads as an epoch.
   pl->res_off = size_t(world) * n_tiles * (size_t(RP_TOKB) * bh * 4);
-  pl->ll_off = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
-  pl->par_need = pl->ll_off + 2 * pl->res_off;
+  const size_t regular = pl->res_off + size_t(n_tiles) * (size_t(RP_TOKB) * bh * 2);
+  pl->reg_need = mode == 3 ? 0 : regular;
+  pl->ll_need = mode == 3 ? 2 * pl->res_off : 0;
   return NVLLM_OK;
 }
 
@@ -593,22 +632,38 @@ using namespace nvllm;
 
 extern "C" {
 
-size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens, int32_t in_features_per_rank,
-                                    int32_t out_features) {
-  // worst case of the shape-only plan over every token count and both feature tiles (a k split forced through
+int nvllm_rowparallel_comm_layout(int32_t world, int32_t max_tokens, int32_t in_features_per_rank,
+                                  int32_t out_features, size_t* header_bytes_out, size_t* regular_bytes_out,
+                                  size_t* flag_in_data_bytes_out) {
+  // worst case of the shape-only plan over every token count and both feature tiles (a k split or mode forced through
   // nvllm_rowparallel_set_plan is honoured: size the buffer after forcing it)
   if (max_tokens > RP_MAX_TOKENS) max_tokens = RP_MAX_TOKENS;
   const int saved_bh = g_force_bh;
-  size_t need = 0;
+  size_t reg = 0, ll = 0;
+  bool any = false;
   for (int n = 1; n <= max_tokens; ++n)
     for (int bh = 32; bh <= 64; bh += 32) {
       RpPlan pl;
       g_force_bh = bh;
-      if (rp_plan(n, in_features_per_rank, out_features, world, &pl) == NVLLM_OK && pl.par_need > need)
-        need = pl.par_need;
+      if (rp_plan(n, in_features_per_rank, out_features, world, &pl) != NVLLM_OK) continue;
+      any = true;
+      if (pl.reg_need > reg) reg = pl.reg_need;
+      if (pl.ll_need > ll) ll = pl.ll_need;
     }
   g_force_bh = saved_bh;
-  return need ? RP_DATA_OFF + 2 * need : 0;
+  if (!any) return NVLLM_ERR_UNSUPPORTED;
+  if (header_bytes_out) *header_bytes_out = RP_DATA_OFF;
+  if (regular_bytes_out) *regular_bytes_out = reg;
+  if (flag_in_data_bytes_out) *flag_in_data_bytes_out = ll;
+  return NVLLM_OK;
+}
+
+size_t nvllm_rowparallel_comm_bytes(int32_t world, int32_t max_tokens, int32_t in_features_per_rank,
+                                    int32_t out_features) {
+  size_t hdr = 0, reg = 0, ll = 0;
+  if (nvllm_rowparallel_comm_layout(world, max_tokens, in_features_per_rank, out_features, &hdr, &reg, &ll) != NVLLM_OK)
+    return 0;
+  return hdr + 2 * (reg + ll);
 }
 
 int nvllm_tp_comm_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out) {
@@ -693,6 +748,14 @@ int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* err
   return NVLLM_OK;
 }
 
+int nvllm_rowparallel_poll_error(uint32_t* error_out, int32_t clear) {
+  if (!error_out) return NVLLM_ERR_BAD_ARG;
+  uint32_t* w = rp_host_error_word();
+  *error_out = w ? *reinterpret_cast<volatile uint32_t*>(w) : 0u;
+  if (w && clear) *reinterpret_cast<volatile uint32_t*>(w) = 0u;
+  return NVLLM_OK;
+}
+
 int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit, int32_t mode, int64_t timeout_ms) {
   if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64)) return NVLLM_ERR_BAD_ARG;
   if (ksplit < 0 || ksplit > RP_MAX_KSPLIT || (ksplit & (ksplit - 1))) return NVLLM_ERR_BAD_ARG;
@@ -730,7 +793,7 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   RpPlan pl;
   int st = rp_plan(n_tokens, in_features_per_rank, out_features, world, &pl);
   if (st != NVLLM_OK) return st;
-  if (comm_bytes < RP_DATA_OFF + 2 * pl.par_need) return NVLLM_ERR_WORKSPACE;
+  if (comm_bytes < RP_DATA_OFF + 2 * (pl.reg_need + pl.ll_need + 16)) return NVLLM_ERR_WORKSPACE;
 
   // every CTA of the grid must be co-resident (cross-rank waits inside the kernel): shrink the cluster while the
   // device cannot hold all of them at once
@@ -758,8 +821,9 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   p.h_tiles = pl.h_tiles; p.n_tiles = pl.n_tiles; p.mode = pl.mode;
   p.par_bytes = (comm_bytes - RP_DATA_OFF) / 2 / 16 * 16;
   p.res_off = pl.res_off;
-  p.ll_off = pl.ll_off;
+  p.ll_off = (p.par_bytes - pl.ll_need) / 16 * 16;   // end-anchored: see rp_plan
   p.timeout_ns = g_timeout_ns;
+  p.host_err = rp_host_error_word();
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, pl.n_tiles * pl.ksplit, pl.ksplit, pl.smem, static_cast<cudaStream_t>(stream));

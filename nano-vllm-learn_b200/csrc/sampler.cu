@@ -301,14 +301,7 @@ extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int3
   if (static_cast<size_t>(bs) * sizeof(int) > kCounterBytes) return NVLLM_ERR_UNSUPPORTED;
   if (!workspace || workspace_bytes < nvllm_sample_workspace_bytes(bs) || !aligned16(workspace)) return NVLLM_ERR_WORKSPACE;
 
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
-      v = 148;
-    sms = v;
-  }
+  const int sms = device_sm_count();
   const int vec = 16 / logits_elem_bytes;
   // one resident wave (__launch_bounds__ guarantees four CTAs per SM) split across the batch, never 1.x waves;
   // a chunk is a whole number of 16-byte vectors

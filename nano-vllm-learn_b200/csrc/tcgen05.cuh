@@ -4,6 +4,7 @@
 #pragma once
 
 #include <cuda.h>
+#include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace nvllm {
@@ -38,12 +39,44 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded spin: a protocol bug must not hang the GPU box.  ~2^26 polls (several seconds) then trap.
+// Bounded spin: a protocol bug must neither hang the GPU box nor kill the CUDA context.  After kMbarTimeoutNs
+// the waiter latches an error word (one per translation unit, read and cleared by the host through
+// tc_error_fetch) and returns as if the barrier had completed; every other wait of the grid sees the latch at
+// its next check and returns too, so the launch drains quickly with undefined results and the HOST reports the
+// failure (nvllm_varlen_prefill_error) instead of a device trap poisoning the process.
+static __device__ unsigned int g_tc_error_latch = 0;
+constexpr unsigned long long kMbarTimeoutNs = 2000000000ull;   // 2 s; a legitimate wait is microseconds
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
+  unsigned long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    if ((++spins & 0xFFFu) != 0u) continue;
+    // slow path, once per 4096 failed polls
+    if (*reinterpret_cast<volatile unsigned int*>(&g_tc_error_latch) != 0u) return;
+    const unsigned long long now = global_timer_ns();
+    if (t0 == 0) t0 = now;
+    if (now - t0 > kMbarTimeoutNs) {
+      atomicCAS(&g_tc_error_latch, 0u, 0x80000000u | (bar & 0xFFFFu) | ((parity & 1u) << 16));
+      return;
+    }
   }
+}
+// Host side: returns and clears the latch of THIS translation unit on the current device (synchronises).
+inline cudaError_t tc_error_fetch(unsigned int* out) {
+  unsigned int v = 0;
+  cudaError_t e = cudaMemcpyFromSymbol(&v, g_tc_error_latch, sizeof(v));
+  if (e != cudaSuccess) return e;
+  *out = v;
+  if (v != 0u) {
+    const unsigned int zero = 0u;
+    e = cudaMemcpyToSymbol(g_tc_error_latch, &zero, sizeof(zero));
+  }
+  return e;
 }
 
 // One lane of a fully converged warp.  The TMA / MMA roles run warp-wide (uniform control flow, so descriptors

@@ -9,6 +9,8 @@
 // 64 keys per step, four warps of 16 rows, K/V tiles double-buffered with cp.async.  The default path is the
 // tcgen05/TMEM kernel in prefill_tcgen05.cu; this kernel stays as the cross-check (variant 0) and as the
 // path taken when no TMA bounds are given or the driver cannot encode tensor maps.
+#include <atomic>
+
 #include "common.cuh"
 #include "prefill_params.cuh"
 
@@ -236,10 +238,28 @@ __global__ void __launch_bounds__(kPrefillThreads) varlen_prefill_mma_kernel(con
 }
 
 static int g_prefill_variant = -1;
+static std::atomic<int> g_last_path{-1};          // 1 = tcgen05, 0 = mma.sync
+static std::atomic<int64_t> g_path_count[2];
+static void note_path(int path) {
+  g_last_path.store(path, std::memory_order_relaxed);
+  g_path_count[path].fetch_add(1, std::memory_order_relaxed);
+}
 
 }  // namespace nvllm
 
 extern "C" {
+
+int32_t nvllm_varlen_prefill_last_path(void) { return nvllm::g_last_path.load(std::memory_order_relaxed); }
+int64_t nvllm_varlen_prefill_path_count(int32_t path) {
+  return (path == 0 || path == 1) ? nvllm::g_path_count[path].load(std::memory_order_relaxed) : -1;
+}
+int nvllm_varlen_prefill_error(uint32_t* code_out) {
+  if (!code_out) return NVLLM_ERR_BAD_ARG;
+  unsigned int v = 0;
+  const int rc = nvllm::prefill_tcgen05_error_fetch(&v);
+  *code_out = v;
+  return rc;
+}
 
 int nvllm_varlen_prefill_set_variant(int32_t variant) {
   if (variant < -1 || variant > 1) return NVLLM_ERR_BAD_ARG;
@@ -292,18 +312,18 @@ int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride, const v
   if (g_prefill_variant != 0) {  // default (-1) and 1: tcgen05/TMEM kernel; 0 forces the mma.sync tile kernel
     bool handled = false;
     int rc = launch_prefill_tcgen05(p, batch, max_seqlen_q, max_seqlen_k, st, &handled);
+    if (rc == NVLLM_OK && handled) note_path(1);
     if (rc != NVLLM_OK || handled) return rc;
   }
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(varlen_prefill_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kPrefillSmem);
-    if (e != cudaSuccess) return record_cuda_error(e);
-    configured = true;
-  }
+  static PerDeviceOnce configured;
+  cudaError_t e0 = once_per_device(configured, [] {
+    return cudaFuncSetAttribute(varlen_prefill_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPrefillSmem);
+  });
+  if (e0 != cudaSuccess) return record_cuda_error(e0);
   dim3 grid((max_seqlen_q + kBM - 1) / kBM, num_q_heads, batch);
   varlen_prefill_mma_kernel<<<grid, kPrefillThreads, kPrefillSmem, st>>>(p);
   note_launch();
+  note_path(0);
   return record_cuda_error(cudaGetLastError());
 }
 

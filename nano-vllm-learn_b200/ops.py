@@ -56,6 +56,27 @@ def set_prefill_variant(variant: int) -> None:
     _lib.check(_lib.load().nvllm_varlen_prefill_set_variant(variant), "set_prefill_variant")
 
 
+PREFILL_KERNEL_NAMES = {1: "prefill_tcgen05_kernel", 0: "varlen_prefill_mma_kernel", -1: "none"}
+
+
+def prefill_last_path() -> int:
+    """1 = the tcgen05/TMEM kernel served the last flash_attn_varlen_func call, 0 = the mma.sync kernel, -1 = none yet."""
+    return int(_lib.load().nvllm_varlen_prefill_last_path())
+
+
+def prefill_path_count(path: int) -> int:
+    return int(_lib.load().nvllm_varlen_prefill_path_count(path))
+
+
+def prefill_error() -> int:
+    """mbarrier-timeout latch of the tcgen05 prefill kernel on the current device (0 = none); clears it.
+    Synchronises the device: not for use under graph capture."""
+    import ctypes
+    code = ctypes.c_uint32(0)
+    _lib.check(_lib.load().nvllm_varlen_prefill_error(ctypes.byref(code)), "varlen_prefill_error")
+    return int(code.value)
+
+
 def set_decode_variant(variant: int) -> None:
     _lib.check(_lib.load().nvllm_paged_decode_set_variant(variant), "set_decode_variant")
 

@@ -54,13 +54,16 @@ class TPComm:
     def required_bytes(world: int, shapes: list[tuple[int, int]], max_tokens: int = MAX_TOKENS) -> int:
         """Buffer size covering every (in_features_per_rank, out_features) in `shapes` (pure host arithmetic)."""
         lib = _lib.load()
-        need = 0
+        hdr, reg, ll = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+        max_reg = max_ll = 0
         for k, h in shapes:
-            b = int(lib.nvllm_rowparallel_comm_bytes(world, max_tokens, k, h))
-            if b == 0:
+            if lib.nvllm_rowparallel_comm_layout(world, max_tokens, k, h, ctypes.byref(hdr), ctypes.byref(reg),
+                                                 ctypes.byref(ll)) != 0:
                 raise ValueError(f"rowparallel: unsupported shape in_features_per_rank={k} out_features={h} world={world}")
-            need = max(need, b)
-        return need
+            max_reg, max_ll = max(max_reg, reg.value), max(max_ll, ll.value)
+        # the flag-in-data inbox sits at the END of each epoch parity, everything else at its start: sized so the
+        # largest of each, taken over all shapes sharing the buffer, never overlap
+        return hdr.value + 2 * (max_reg + max_ll) if shapes else 0
 
     @classmethod
     def from_process_group(cls, nbytes: int, group=None) -> "TPComm":
@@ -141,6 +144,24 @@ class TPComm:
         return ep.value, err.value
 
 
+def poll_error(clear: bool = False) -> int:
+    """Timeout latch of the fused kernels launched by this process (0 = none): a mapped host word, no CUDA call."""
+    err = ctypes.c_uint32()
+    _lib.check(_lib.load().nvllm_rowparallel_poll_error(ctypes.byref(err), 1 if clear else 0), "rowparallel_poll_error")
+    return err.value
+
+
+def raise_on_timeout() -> None:
+    """Turn a latched peer timeout into an exception, as NCCL would: called after every eager fused
+    forward and after every graph replay by the runner glue.  Costs one ctypes call and one host memory read."""
+    err = poll_error()
+    if err:
+        poll_error(clear=True)
+        raise _lib.NvllmError(f"fused RowParallelLinear all-reduce: a tensor-parallel peer never arrived (tile {err - 1}); "
+                              f"hidden states of that step are undefined.  NVLLM_FUSED_ALLREDUCE_TIMEOUT_MS sets the "
+                              f"wait (default 20000), NVLLM_FUSED_ALLREDUCE=0 restores the NCCL all-reduce")
+
+
 _COMM: TPComm | None = None
 _SHAPES: set[tuple[int, int]] = set()
 _ENABLED = False
@@ -164,6 +185,9 @@ def configure(cuda_backend: bool) -> None:
     else:
         want = env != "0"
     _ENABLED = bool(cuda_backend) and want
+    tmo = os.environ.get("NVLLM_FUSED_ALLREDUCE_TIMEOUT_MS")
+    if tmo is not None and int(tmo) > 0:
+        ops.rowparallel_set_plan(timeout_ms=int(tmo))
     release()
 
 
@@ -220,7 +244,10 @@ def install(RowParallelLinear) -> None:
         if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > self._nvllm_fused_max or \
                 x.dtype != torch.bfloat16 or not x.is_cuda:
             return ref_forward(self, x)
-        return ops.rowparallel_linear_allreduce(x, self.weight, self.bias, get_comm())
+        y = ops.rowparallel_linear_allreduce(x, self.weight, self.bias, get_comm())
+        if not torch.cuda.is_current_stream_capturing():
+            raise_on_timeout()   # a timeout of an EARLIER launch (this one is still running): one host memory read
+        return y
 
     RowParallelLinear.__init__ = __init__
     RowParallelLinear.forward = forward

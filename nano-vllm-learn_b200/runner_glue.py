@@ -24,6 +24,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import rowparallel_cuda as _rp
 
 _I32P = ctypes.POINTER(ctypes.c_int32)
 
@@ -261,7 +262,10 @@ class RunnerGlue:
         # The table of a running batch changes only when a block is appended or the batch changes; between two
         # prefills a (row count, layout, per-row length, per-row last block) signature pins the content of this
         # ring slot, so the common step rewrites nothing but ids / positions / lens / slots.
-        sig = (rows, cols, bs, width, tuple(map(len, tables)), tuple(last_blocks))
+        # Sequence identity is part of it: a batch where one running sequence was swapped for another of equal length
+        # and equal last block must not inherit the staged table (tests/test_runner_glue.py::test_decode_swap...).
+        sig = (rows, cols, bs, width, tuple(getattr(s, "seq_id", id(s)) for s in seqs), tuple(map(len, tables)),
+               tuple(last_blocks))
         if self._slot_sig[slot_idx] != sig:
             self._slot_sig[slot_idx] = sig
             if gbs is not None:
@@ -341,6 +345,8 @@ def install(model_runner_cls, set_context: Callable, get_context: Callable, rese
             return self.model.compute_logits(self.model(input_ids, positions))
         # prepare_decode already staged ids/positions/context in the captured buffers of bucket `gbs`
         self.graphs[gbs].replay()
+        if _rp.enabled():
+            _rp.raise_on_timeout()   # fused all-reduce peer timeout of an earlier replay -> exception (one host read)
         return self.model.compute_logits(self.graph_vars["outputs"][:bs])
 
     @torch.inference_mode()

@@ -38,6 +38,7 @@ def test_tcgen05_prefill_vs_oracle_and_fixture(ops, name):
     g = _cuda(c)
     got = ops.flash_attn_varlen_func(g["q"], g["k"], g["v"], c["max_seqlen_q"], g["cu_seqlens_q"], c["max_seqlen_k"],
                                      g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True)
+    assert ops.prefill_last_path() == 1, "the tcgen05 kernel did not serve this call"
     assert _maxerr(got, want) <= TOL
     gold = cases.from_bits(np.load(os.path.join(GOLD, f"prefill_{name}.npz"))["out"])
     assert _maxerr(got, gold) <= TOL
@@ -52,6 +53,7 @@ def test_tcgen05_prefix_prefill_vs_oracle(ops, name):
     got = ops.flash_attn_varlen_func(g["q"], g["k_cache"], g["v_cache"], c["max_seqlen_q"], g["cu_seqlens_q"],
                                      c["max_seqlen_k"], g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True,
                                      block_table=g["block_tables"])
+    assert ops.prefill_last_path() == 1, "the tcgen05 kernel did not serve this call"
     assert _maxerr(got, want) <= TOL
 
 
@@ -67,9 +69,12 @@ def test_tcgen05_full_size_vs_mma_kernel(ops):
     v = fused[:, hkv * 128:].view(total, hkv, 128)
     cu = torch.arange(0, total + 1, L, dtype=torch.int32, device=DEV)
     scale = 128 ** -0.5
+    n1, n0 = ops.prefill_path_count(1), ops.prefill_path_count(0)
     out = ops.flash_attn_varlen_func(q, k, v, L, cu, L, cu, softmax_scale=scale, causal=True)
+    assert ops.prefill_last_path() == 1 and ops.prefill_path_count(1) == n1 + 1
     ops.set_prefill_variant(0)
     ref = ops.flash_attn_varlen_func(q, k, v, L, cu, L, cu, softmax_scale=scale, causal=True)
+    assert ops.prefill_last_path() == 0 and ops.prefill_path_count(0) == n0 + 1
     ops.set_prefill_variant(1)
     assert _maxerr(out, ref) <= 8e-3
     i = 11
@@ -90,3 +95,18 @@ def test_tcgen05_ragged_batch_vs_mma_kernel(ops):
     out = ops.flash_attn_varlen_func(q, k, v, max(lens), cu, max(lens), cu, softmax_scale=128 ** -0.5)
     want = orc.varlen_prefill_ref(q.cpu(), k.cpu(), v.cpu(), cu.cpu(), cu.cpu(), 128 ** -0.5)
     assert _maxerr(out, want) <= TOL
+
+
+def test_default_variant_is_tcgen05_and_no_timeout_latched(lib):
+    """The library default (variant -1) must run the tcgen05 kernel on these shapes, and no mbarrier wait of
+    any prefill launch in this process may have timed out (the kernel latches instead of trapping)."""
+    from nano_vllm_learn_b200 import ops as _ops
+    _ops.set_prefill_variant(-1)
+    c = cases.make_prefill_case(next(iter(cases.PREFILL_CASES)))
+    g = _cuda(c)
+    _ops.flash_attn_varlen_func(g["q"], g["k"], g["v"], c["max_seqlen_q"], g["cu_seqlens_q"], c["max_seqlen_k"],
+                                g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True)
+    assert _ops.prefill_last_path() == 1
+    assert _ops.PREFILL_KERNEL_NAMES[_ops.prefill_last_path()] == "prefill_tcgen05_kernel"
+    torch.cuda.synchronize()
+    assert _ops.prefill_error() == 0

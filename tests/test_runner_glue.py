@@ -139,6 +139,31 @@ def test_ring_reuse_does_not_alias_previous_step(lib):
     assert ctx.args.slot_mapping.tolist() == [7 * 256 + 43]
 
 
+@pytest.mark.parametrize("graphs", [False, True])
+def test_decode_swap_of_equal_shaped_sequence_restages_table(lib, graphs):
+    """two batches whose per-row lengths and last blocks agree but whose sequences (and so the
+    earlier table entries) differ must not share a staged block table.  Every ring slot is visited."""
+    ctx = Ctx()
+    g = _glue(lib, ctx)
+    if graphs:
+        g.graph_bs = [1, 2, 4, 8]
+
+    def seq(seq_id, table):
+        s = Seq([7], table, 0, 300, 7)
+        s.seq_id = seq_id
+        return s
+
+    a = [seq(0, [2, 9]), seq(1, [3, 8])]
+    b = [seq(0, [2, 9]), seq(5, [6, 8])]          # row 1 swapped: same length, same LAST block, different first block
+    for step in range(2 * g.RING + 1):
+        batch = a if step % 2 == 0 else b
+        g.prepare_decode(batch)
+        want = gorc.prepare_decode_ref(batch)
+        assert torch.equal(ctx.args.block_tables, want["block_tables"]), step
+        assert torch.equal(ctx.args.slot_mapping, want["slot_mapping"])
+        assert torch.equal(ctx.args.context_lens, want["context_lens"])
+
+
 def test_live_reference_trace(lib):
     """Drive the REAL BlockManager/Sequence/ModelRunner.prepare_* (unmodified) side by side with the glue."""
     root = gorc.find_reference_root()

@@ -1,7 +1,8 @@
 // Read-bandwidth probe used to bound the decode kernel (tools/membench.py): streams a buffer with either the
 // decode kernel's access shape (256-byte (token, kv-head) rows at a token stride of Hkv * 256 bytes, one
 // head per CTA) or fully contiguous 512-byte warp reads.  Not on the product path.
-#include "common.cuh"
+#include "../../nano-vllm-learn_b200/csrc/common.cuh"
+#include "../../include/nvllm_tools.h"
 
 namespace nvllm {
 

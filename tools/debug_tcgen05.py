@@ -19,7 +19,7 @@ def stats(name, got, want):
 
 def main():
     dev = "cuda:0"
-    lib = _lib.load()
+    lib = _lib.load_tools()   # python nano-vllm-learn_b200/build.py --tools
     torch.manual_seed(0)
     L = int(sys.argv[1]) if len(sys.argv) > 1 else 256
     hq, hkv, d = 4, 2, 128

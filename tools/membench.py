@@ -10,7 +10,7 @@ import torch  # noqa: E402
 
 from nano_vllm_learn_b200 import _lib  # noqa: E402
 
-lib = _lib.load()
+lib = _lib.load_tools()   # python nano-vllm-learn_b200/build.py --tools
 dev = torch.device("cuda", 0)
 nbytes = 2 << 30
 bufs = [torch.empty(nbytes, dtype=torch.uint8, device=dev).random_(0, 255) for _ in range(2)]

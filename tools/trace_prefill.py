@@ -10,7 +10,7 @@ import torch  # noqa: E402
 from nano_vllm_learn_b200 import _lib, ops  # noqa: E402
 
 dev = "cuda:0"
-lib = _lib.load()
+lib = _lib.load_tools()   # python nano-vllm-learn_b200/build.py --tools
 L = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 MODE = int(sys.argv[2]) if len(sys.argv) > 2 else 0  # bit0 no exp/P stores, bit1 no S loads, bit2 no K/V TMA
 hq, hkv, d = 32, 8, 128
