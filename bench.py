@@ -56,13 +56,19 @@ def parse_args():
     ap.add_argument("--ctx", type=int, default=4096)
     ap.add_argument("--hq", type=int, default=16)
     ap.add_argument("--hkv", type=int, default=8)
-    ap.add_argument("--splits", type=int, default=0, help="0 = library plan")
+    ap.add_argument("--splits", type=int, default=None,
+                    help="default: library plan; 0 / -P = balanced persistent grid (P CTAs); >= 1 = fixed split-KV grid")
     ap.add_argument("--variant", type=int, default=-1)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-tp", action="store_true")
     ap.add_argument("--no-prefill", action="store_true")
     ap.add_argument("--cpu-sample-bs", type=int, default=2)
+    ap.add_argument("--no-flash", action="store_true", help="skip the flash-attn comparator legs (vs_flash)")
+    ap.add_argument("--no-long-ctx", action="store_true")
+    ap.add_argument("--no-fused-allreduce", action="store_true")
+    ap.add_argument("--no-tp-e2e", action="store_true", help="skip the bounded end-to-end engine run (bench_my protocol)")
+    ap.add_argument("--tp-e2e-timeout", type=int, default=420)
     return ap.parse_args()
 
 
@@ -139,6 +145,55 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def time_back_to_back(fn, n_sets, launches=60, warm=6):
+    """Per-launch device time of `fn(i)` (i rotates over `n_sets` input copies whose total exceeds L2): `launches`
+    launches queued back to back on the current stream with a CUDA event between neighbours, ONE synchronise at the
+    end -- the host runs ahead of the GPU, so no launch latency and no single-launch event overhead is timed.
+    Returns min / median / max / mean in microseconds."""
+    for i in range(warm):
+        fn(i % n_sets)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(launches + 1)]
+    torch.cuda._sleep(2_000_000)          # ~1 ms of GPU work: the queue is full before the first timed launch starts
+    ev[0].record()
+    for i in range(launches):
+        fn(i % n_sets)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    us = sorted(ev[i].elapsed_time(ev[i + 1]) * 1e3 for i in range(launches))
+    return {"min": round(us[0], 2), "median": round(statistics.median(us), 2), "max": round(us[-1], 2),
+            "mean": round(sum(us) / len(us), 2), "launches": launches}
+
+
+def time_in_graph(fn, n_sets, reps=2, iters=5):
+    """Per-launch device time inside ONE CUDA graph of n_sets*reps launches (how the engine replays a decode step:
+    one launch per layer, each on its own cache)."""
+    n = n_sets * reps
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(n_sets):
+            fn(i)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(n):
+            fn(i % n_sets)
+    g.replay()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e3 / n)
+    del g
+    return round(statistics.median(ts), 2)
+
+
 # --------------------------------------------------------------------------------------- cuda arm
 class Workload:
     """Per-rank synthetic decode workload resident in HBM."""
@@ -194,7 +249,7 @@ def run_cuda(args):
 
     wl = Workload(dev, args.layers, args.bs, args.ctx, args.hq, args.hkv, seed=rank)
     scale = D ** -0.5
-    splits = args.splits if args.splits > 0 else ops.plan_num_splits(wl.bs, wl.hkv, wl.tables.size(1) * BLOCK)
+    splits = args.splits if args.splits is not None else ops.plan_num_splits(wl.bs, wl.hq, wl.hkv, wl.tables.size(1) * BLOCK)
     out = torch.empty(wl.bs, wl.hq, D, dtype=torch.bfloat16, device=dev)
     ws_bytes = ops.decode_workspace_bytes(wl.bs, wl.hq, D, splits)
     ws = torch.zeros(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
@@ -248,7 +303,8 @@ def run_cuda(args):
     peak, peak_src = peaks()
     kern_us = statistics.mean(kern_ms) * 1e3
     achieved = wl.bytes_decode / (kern_us * 1e-6) / 1e9
-    roofline = {"bound": "hbm", "kernel": "paged_decode_kernel" + ("+combine" if splits > 1 else ""),
+    kname = "paged_decode_balanced_kernel" if splits <= 0 else "paged_decode_kernel" + ("+combine" if splits > 1 else "")
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                 "frac_of_nominal_8TBs": round(achieved / 8000.0, 4), "peak_source": peak_src,
                 "us_per_launch": round(kern_us, 2), "algorithmic_bytes_per_launch": wl.bytes_decode,
@@ -269,15 +325,31 @@ def run_cuda(args):
         e2e["h2d_bytes_per_step"] *= world
         e2e["d2h_bytes_per_step"] *= world
 
+    cfg_layers, cfg_bs, cfg_hq, cfg_hkv, bytes_step = wl.layers, wl.bs, wl.hq, wl.hkv, wl.bytes_step
+    vs_flash = None
+    if rank == 0 and not args.no_flash:
+        vs_flash = run_vs_flash_headline(wl, ops, scale, splits, out, ws)
+
     tp_strong = None
+    del wl.kv
+    torch.cuda.empty_cache()
     if not args.no_tp:
-        del wl.kv
-        torch.cuda.empty_cache()
         tp_strong = run_tp_point(args, dev, world, rank, ops, dist)
+
+    long_ctx = None
+    if rank == 0 and not args.no_long_ctx:
+        long_ctx = run_long_ctx(args, dev, ops)
 
     prefill = None
     if rank == 0 and not args.no_prefill:
-        prefill = run_prefill_points(dev, ops)
+        prefill = run_prefill_points(dev, ops, with_flash=not args.no_flash)
+
+    fused = None
+    if dist is not None and not args.no_fused_allreduce:
+        try:
+            fused = run_fused_allreduce(args, dev, rank, world, ops, dist)
+        except Exception as e:   # a comparator leg must not take the headline line down with it
+            fused = {"failed": f"{type(e).__name__}: {e}"[:300]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -285,23 +357,35 @@ def run_cuda(args):
 
     if dist is not None:
         dist.barrier()
-    if rank == 0:
-        line = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": {"workload": f"Qwen3-0.6B-shape decode attention hot path (store_kvcache + paged GQA decode) "
-                                       f"x {wl.layers} layers, bs={wl.bs}, ctx={args.ctx}, {wl.hq}q/{wl.hkv}kv heads, "
-                                       f"head_dim 128, block 256 (bench_my worst point, BASELINE configs[1])",
-                           "per_gpu_algorithmic_bytes_per_step": wl.bytes_step,
-                           "parallelism": f"{world} rank(s), (sequence, kv-head) shards, no collective",
-                           "l2": "per-layer caches total %.1f GB >> 126 MB L2; no flush needed" %
-                                 (wl.layers * wl.bs * ((args.ctx + BLOCK - 1) // BLOCK) * BLOCK * wl.hkv * D * 4 / 1e9),
-                           "timing": "CUDA events on the launch stream, max over ranks"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
-                "cpu_baseline": cpu, "tp_strong": tp_strong, "prefill": prefill}
-        print(json.dumps(line), flush=True)
-    if dist is not None:
         dist.destroy_process_group()
+    del wl
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return
+
+    tp_e2e = None
+    if not args.no_tp_e2e and os.environ.get("NVLLM_BENCH_TP_E2E", "1") != "0":
+        time.sleep(3.0 if world > 1 else 0.0)    # the other ranks are exiting and releasing their GPUs
+        try:
+            tp_e2e = run_tp_e2e(args, world)
+        except Exception as e:
+            tp_e2e = {"failed": f"{type(e).__name__}: {e}"[:300]}
+
+    line = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"Qwen3-0.6B-shape decode attention hot path (store_kvcache + paged GQA decode) "
+                                   f"x {cfg_layers} layers, bs={cfg_bs}, ctx={args.ctx}, {cfg_hq}q/{cfg_hkv}kv heads, "
+                                   f"head_dim 128, block 256 (bench_my worst point, BASELINE configs[1])",
+                       "per_gpu_algorithmic_bytes_per_step": bytes_step,
+                       "parallelism": f"{world} rank(s), (sequence, kv-head) shards, no collective",
+                       "l2": "per-layer caches total %.1f GB >> 126 MB L2; no flush needed" %
+                             (cfg_layers * cfg_bs * ((args.ctx + BLOCK - 1) // BLOCK) * BLOCK * cfg_hkv * D * 4 / 1e9),
+                       "timing": "CUDA events on the launch stream, max over ranks"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
+            "cpu_baseline": cpu, "vs_flash": vs_flash, "tp_strong": tp_strong, "long_ctx": long_ctx,
+            "prefill": prefill, "fused_allreduce": fused, "tp_e2e": tp_e2e}
+    print(json.dumps(line), flush=True)
 
 
 def load_traffic():
@@ -392,55 +476,145 @@ def run_e2e(args, wl, dev, Attention, set_context, reset_context, scale, dist):
                    "H2D / compute / D2H on three streams"}
 
 
-def run_tp_point(args, dev, world, rank, ops, dist):
-    """configs[3]: Qwen3-8B-shape decode, bs=128 ctx=4096, 32q/8kv heads split `world` ways (strong scaling)."""
-    if 8 % world != 0:
-        return None
-    hq, hkv, bs, ctx, layers = 32 // world, 8 // world, 128, 4096, 4
-    wl = Workload(dev, layers, bs, ctx, hq, hkv, seed=100 + rank)
+def _decode_sets(dev, bs, ctx, hq, hkv, width, min_total_bytes, max_sets, seed):
+    """Independent (q, k_cache, v_cache, lens, table) copies so that consecutive launches never re-read L2."""
+    pages = (ctx + BLOCK - 1) // BLOCK
+    one = bs * pages * BLOCK * hkv * D * 2 * 2
+    n_sets = max(2, min(max_sets, -(-min_total_bytes // one)))
+    sets = []
+    g = torch.Generator(device=dev).manual_seed(seed)
+    for _ in range(n_sets):
+        nblk = bs * pages
+        kc = torch.empty(nblk, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+        vc = torch.empty(nblk, BLOCK, hkv, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+        q = torch.empty(bs, hq, D, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+        tab = torch.randperm(nblk, generator=g, device=dev).to(torch.int32).view(bs, pages)
+        if width and width > pages:     # captured-graph layout: zero padded to ceil(max_model_len / 256) columns
+            wide = torch.zeros(bs, width, dtype=torch.int32, device=dev)
+            wide[:, :pages] = tab
+            tab = wide
+        sets.append((q, kc, vc, tab))
+    lens = torch.full((bs,), ctx, dtype=torch.int32, device=dev)
+    return sets, lens, decode_bytes(bs, [ctx] * bs, hq, hkv)
+
+
+def _time_decode_shape(dev, ops, bs, ctx, hq, hkv, width, seed, flash=None, min_total=1 << 30, max_sets=16):
+    sets, lens, nbytes = _decode_sets(dev, bs, ctx, hq, hkv, width, min_total, max_sets, seed)
+    n_sets = len(sets)
     scale = D ** -0.5
-    splits = ops.plan_num_splits(bs, hkv, wl.tables.size(1) * BLOCK)
+    splits = ops.plan_num_splits(bs, hq, hkv, sets[0][3].size(1) * BLOCK)
     out = torch.empty(bs, hq, D, dtype=torch.bfloat16, device=dev)
     ws = torch.zeros(max(ops.decode_workspace_bytes(bs, hq, D, splits), 16), dtype=torch.uint8, device=dev)
 
-    def one(l):
-        ops.flash_attn_with_kvcache(wl.q[l].view(bs, hq, D), wl.kv[0, l], wl.kv[1, l], wl.lens, wl.tables,
-                                    softmax_scale=scale, num_splits=splits, out=out, workspace=ws)
+    def one(i):
+        q, kc, vc, tab = sets[i]
+        ops.flash_attn_with_kvcache(q, kc, vc, lens, tab, softmax_scale=scale, num_splits=splits, out=out, workspace=ws)
 
-    for _ in range(3):
-        one(0)
-    times = []
-    for i in range(12):   # rotate over 4 distinct caches (>= 1.07 GB in total even at tp=8): nothing is re-read from L2
-        torch.cuda._sleep(300_000)   # GPU busy while the host queues the launch: host launch latency is not timed
-        a = torch.cuda.Event(enable_timing=True)
-        b = torch.cuda.Event(enable_timing=True)
-        a.record()
-        one(i % layers)
-        b.record()
-        torch.cuda.synchronize()
-        times.append(a.elapsed_time(b))
-    us = statistics.median(times) * 1e3
-    t = torch.tensor([us], dtype=torch.float64, device=dev)
+    t = time_back_to_back(one, n_sets)
+    res = {"us": t, "graph_us_per_launch": time_in_graph(one, n_sets), "algorithmic_bytes": nbytes, "num_splits": splits,
+           "input_copies_rotated": n_sets}
+    if flash is not None:
+        def fl(i):
+            q, kc, vc, tab = sets[i]
+            flash(q.unsqueeze(1), kc, vc, cache_seqlens=lens, block_table=tab, softmax_scale=scale, causal=True)
+        try:
+            res["flash_us"] = time_back_to_back(fl, n_sets)
+            res["flash_graph_us_per_launch"] = time_in_graph(fl, n_sets)
+        except Exception as e:   # comparator only
+            res["flash_us"] = f"failed: {type(e).__name__}: {e}"[:200]
+    del sets, out, ws
+    torch.cuda.empty_cache()
+    return res
+
+
+def _flash_decode():
+    try:
+        from flash_attn import flash_attn_with_kvcache
+        return flash_attn_with_kvcache
+    except Exception:
+        return None
+
+
+def run_tp_point(args, dev, world, rank, ops, dist):
+    """configs[3]: Qwen3-8B-shape decode, bs=128 ctx=4096, 32q/8kv heads split `world` ways (strong scaling).
+    60 launches back to back rotating over >= 1 GiB of distinct caches; min / median / max, max over ranks."""
+    if 8 % world != 0:
+        return None
+    hq, hkv, bs, ctx = 32 // world, 8 // world, 128, 4096
+    r = _time_decode_shape(dev, ops, bs, ctx, hq, hkv, 16, seed=100 + rank, flash=None if args.no_flash else _flash_decode(),
+                           min_total=2 << 30, max_sets=8)
+    vals = [r["us"]["median"], r["us"]["min"], r["us"]["max"], r["graph_us_per_launch"]]
+    t = torch.tensor(vals, dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    us = float(t.item())
+    med, mn, mx, gr = (float(x) for x in t.tolist())
     peak, _ = peaks()
-    gbs = wl.bytes_decode / (us * 1e-6) / 1e9
-    return {"workload": f"Qwen3-8B-shape decode op, bs=128 ctx=4096, tp={world}: {hq}q/{hkv}kv heads per GPU",
-            "us_per_launch_max_over_ranks": round(us, 2), "per_gpu_GBps": round(gbs, 1),
-            "aggregate_GBps": round(gbs * world, 1), "frac_of_measured_peak": round(gbs / peak, 4),
-            "num_splits": splits, "l2": "launches rotate over 4 distinct caches, working set >> 126 MB L2"}
+    gbs = r["algorithmic_bytes"] / (med * 1e-6) / 1e9
+    out = {"workload": f"Qwen3-8B-shape decode op, bs=128 ctx=4096, tp={world}: {hq}q/{hkv}kv heads per GPU",
+           "us_per_launch_max_over_ranks": round(med, 2), "us_min": round(mn, 2), "us_max": round(mx, 2),
+           "graph_us_per_launch": round(gr, 2), "per_gpu_GBps": round(gbs, 1), "aggregate_GBps": round(gbs * world, 1),
+           "frac_of_measured_peak": round(gbs / peak, 4), "frac_of_nominal_8TBs": round(gbs / 8000.0, 4),
+           "num_splits": r["num_splits"],
+           "timing": f"median of {r['us']['launches']} back-to-back launches (CUDA event between neighbours), max over ranks",
+           "l2": f"launches rotate over {r['input_copies_rotated']} distinct caches (>= 2 GiB), nothing is re-read from L2"}
+    if isinstance(r.get("flash_us"), dict):
+        out["flash_attn_us_rank0"] = r["flash_us"]["median"]
+    return out
 
 
-def run_prefill_points(dev, ops):
-    """Secondary line: the tcgen05 varlen-prefill kernel against the tensor roofline.
+def run_long_ctx(args, dev, ops):
+    """configs[4]: Qwen3-8B-shape long-context decode, ctx 32768, table width 160 (max_model_len 40960), bs 1/2/4 at
+    tp=1 (32q/8kv) and the tp=8 shard (4q/1kv).  Small batches: the launch is short, so both the back-to-back event
+    timing and the in-graph per-launch time are reported; launches rotate over >= 1 GiB of distinct caches."""
+    peak, _ = peaks()
+    flash = None if args.no_flash else _flash_decode()
+    rows = []
+    for bs, hq, hkv, tp in ((1, 32, 8, 1), (2, 32, 8, 1), (4, 32, 8, 1), (1, 4, 1, 8), (4, 4, 1, 8)):
+        r = _time_decode_shape(dev, ops, bs, 32768, hq, hkv, 160, seed=500 + bs + tp, flash=flash)
+        us = r["us"]["median"]
+        row = {"bs": bs, "ctx": 32768, "heads": f"{hq}q/{hkv}kv (tp={tp} shard)", "us": us, "us_min": r["us"]["min"],
+               "us_max": r["us"]["max"], "graph_us_per_launch": r["graph_us_per_launch"],
+               "GBps": round(r["algorithmic_bytes"] / us / 1e3, 1),
+               "graph_GBps": round(r["algorithmic_bytes"] / r["graph_us_per_launch"] / 1e3, 1),
+               "frac_of_measured_peak": round(r["algorithmic_bytes"] / us / 1e3 / peak, 4),
+               "algorithmic_bytes": r["algorithmic_bytes"], "num_splits": r["num_splits"]}
+        if isinstance(r.get("flash_us"), dict):
+            row["flash_attn_us"] = r["flash_us"]["median"]
+            row["flash_attn_graph_us_per_launch"] = r.get("flash_graph_us_per_launch")
+        rows.append(row)
+    return rows
+
+
+def run_prefill_points(dev, ops, with_flash=True):
+    """Secondary line: the varlen-prefill kernel against the tensor roofline, flash-attn's
+    flash_attn_varlen_func (the reference `flash` backend's call, attention.py:93-96) on the same tensors beside it.
     FLOPs = 4*Hq*128*sum_i[Lq_i*cached_i + Lq_i(Lq_i+1)/2]; peak = measured bf16 burst."""
     peak = 1590.0
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
         with open(path) as f:
             peak = float(json.load(f)["bf16_tflops"])
+    fa = None
+    if with_flash:
+        try:
+            from flash_attn import flash_attn_varlen_func as fa
+        except Exception:
+            fa = None
     out = []
+
+    def med_us(fn):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(10):
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            fn()
+            b_.record()
+            torch.cuda.synchronize()
+            ts.append(a_.elapsed_time(b_))
+        return statistics.median(ts) * 1e3
+
     for name, b, lq, cached, hq, hkv in (("bench.py prefill step: 16 x 1024, 16q/8kv", 16, 1024, 0, 16, 8),
                                          ("prefix cache: 16 x (512 new + 512 cached), 16q/8kv", 16, 512, 512, 16, 8),
                                          ("Qwen3-8B-shape: 4 x 4096, 32q/8kv", 4, 4096, 0, 32, 8)):
@@ -461,21 +635,205 @@ def run_prefill_points(dev, ops):
         o = torch.empty_like(q)
         fl = 4 * hq * D * b * (lq * cached + lq * (lq + 1) // 2)
         fn = lambda: ops.flash_attn_varlen_func(q, k, v, lq, cu_q, lk, cu_k, softmax_scale=D ** -0.5, block_table=tab, out=o)
-        for _ in range(3):
-            fn()
-        ts = []
-        for _ in range(10):
-            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a_.record()
-            fn()
-            b_.record()
-            torch.cuda.synchronize()
-            ts.append(a_.elapsed_time(b_))
-        us = statistics.median(ts) * 1e3
-        out.append({"workload": name, "kernel": "prefill_tcgen05_kernel", "us": round(us, 1),
-                    "achieved": round(fl / us / 1e6, 1), "peak": peak, "unit": "TFLOP/s", "bound": "tensor",
-                    "frac": round(fl / us / 1e6 / peak, 4)})
+        us = med_us(fn)
+        row = {"workload": name, "kernel": ops.PREFILL_KERNEL_NAMES[ops.prefill_last_path()], "us": round(us, 1),
+               "achieved": round(fl / us / 1e6, 1), "peak": peak, "unit": "TFLOP/s", "bound": "tensor",
+               "frac": round(fl / us / 1e6 / peak, 4)}
+        if fa is not None:
+            try:
+                ffn = lambda: fa(q, k, v, max_seqlen_q=lq, cu_seqlens_q=cu_q, max_seqlen_k=lk, cu_seqlens_k=cu_k,
+                                 softmax_scale=D ** -0.5, causal=True, block_table=tab)
+                fus = med_us(ffn)
+                row["flash_attn_us"] = round(fus, 1)
+                row["flash_attn_TFLOPs"] = round(fl / fus / 1e6, 1)
+                row["max_abs_diff_vs_flash_attn"] = round((ffn().float() - o.float()).abs().max().item(), 5)
+            except Exception as e:   # comparator only
+                row["flash_attn_us"] = f"failed: {type(e).__name__}: {e}"[:200]
+        out.append(row)
         del q, k, v, o
+    out.append({"mbarrier_timeout_latch": ops.prefill_error()})
+    return out
+
+
+def run_vs_flash_headline(wl, ops, scale, splits, out, ws):
+    """The headline decode launch (one layer of the bench workload) beside flash-attn's flash_attn_with_kvcache -- the
+    exact call of the reference `flash` backend (attention.py:99-101) -- same tensors, same process, launches rotating
+    over the per-layer caches (30 GB >> L2), back-to-back event timing."""
+    fa = _flash_decode()
+    if fa is None:
+        return {"unavailable": "flash_attn not importable"}
+    n = wl.layers
+
+    def mine(i):
+        ops.flash_attn_with_kvcache(wl.q[i].view(wl.bs, wl.hq, D), wl.kv[0, i], wl.kv[1, i], wl.lens, wl.tables,
+                                    softmax_scale=scale, num_splits=splits, out=out, workspace=ws)
+
+    def theirs(i):
+        return fa(wl.q[i].view(wl.bs, 1, wl.hq, D), wl.kv[0, i], wl.kv[1, i], cache_seqlens=wl.lens,
+                  block_table=wl.tables, softmax_scale=scale, causal=True)
+
+    try:
+        t_f = time_back_to_back(theirs, n, launches=56)
+        t_m = time_back_to_back(mine, n, launches=56)
+        mine(0)
+        diff = (theirs(0).view(wl.bs, wl.hq, D).float() - out.float()).abs().max().item()
+    except Exception as e:
+        return {"failed": f"{type(e).__name__}: {e}"[:200]}
+    return {"decode_us": t_m["median"], "decode_GBps": round(wl.bytes_decode / t_m["median"] / 1e3, 1),
+            "flash_attn_decode_us": t_f["median"], "flash_attn_decode_GBps": round(wl.bytes_decode / t_f["median"] / 1e3, 1),
+            "speedup": round(t_f["median"] / t_m["median"], 3), "max_abs_diff": round(diff, 5),
+            "flash_attn_version": getattr(__import__("flash_attn"), "__version__", "?"),
+            "timing": "median of 56 back-to-back launches each, rotating over the 28 per-layer caches"}
+
+
+def run_fused_allreduce(args, dev, rank, world, ops, dist):
+    """SURVEY §8f rank 2, N > 1 only: the fused RowParallelLinear (GEMM + all-reduce in one launch over NVLink peer
+    memory) beside the reference's `F.linear` + `dist.all_reduce` (nanovllm/layers/linear.py:185-190) on the o_proj /
+    down_proj shards of Qwen3-0.6B and the Qwen3-8B shape at tensor_parallel_size = N.
+    Parity on the box first: every rank's y bit-identical, |y - exact| <= 2^-8 * max|exact| (exact = fp64 contraction
+    all-reduced over the ranks), no timeout latched.  Then device time per call: both arms as CUDA-graph chains of 28
+    calls, CUDA events, max over ranks."""
+    import torch.nn.functional as F
+    from nano_vllm_learn_b200 import rowparallel_cuda as rp
+    shapes = [("qwen3-0.6b o_proj", 2048, 1024), ("qwen3-0.6b down_proj", 3072, 1024),
+              ("qwen3-8b-shape o_proj", 4096, 4096), ("qwen3-8b-shape down_proj", 12288, 4096)]
+    shapes = [sh for sh in shapes if sh[1] % world == 0 and (sh[1] // world) % 64 == 0]
+    ops.rowparallel_set_plan(timeout_ms=5000)
+    comm = rp.TPComm.from_process_group(rp.TPComm.required_bytes(world, [(k // world, h) for _, k, h in shapes]))
+    chain, iters = 28, 5
+    rows, all_ok = [], True
+
+    def reference(x, w):
+        y = F.linear(x, w)
+        dist.all_reduce(y)
+        return y
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(chain):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) * 1e3 / (iters * chain)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        del g
+        return round(float(t.item()), 2)
+
+    for name, k, h in shapes:
+        kr = k // world
+        for n in (1, 16, 64, 256):
+            gen = torch.Generator(device=dev).manual_seed(7000 + 13 * n + k + rank)
+            x = torch.empty(n, kr, dtype=torch.bfloat16, device=dev).normal_(generator=gen)
+            w = (torch.empty(h, kr, dtype=torch.float32, device=dev).normal_(generator=gen) * k ** -0.5).to(torch.bfloat16)
+            y = ops.rowparallel_linear_allreduce(x, w, None, comm)
+            exact = x.double() @ w.double().T
+            dist.all_reduce(exact)
+            torch.cuda.synchronize()
+            scale = exact.abs().max().item()
+            err = (y.double() - exact).abs().max().item()
+            gathered = [torch.empty_like(y) for _ in range(world)]
+            dist.all_gather(gathered, y)
+            same = all(torch.equal(gathered[0].view(torch.int16), t.view(torch.int16)) for t in gathered)
+            err_ref = (reference(x, w).double() - exact).abs().max().item()
+            flag = torch.tensor([1 if (same and err <= 2.0 ** -8 * scale and rp.poll_error() == 0) else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = bool(flag.item())
+            all_ok = all_ok and ok
+            row = {"shard": name, "in_features_per_rank": kr, "out_features": h, "tokens": n, "parity_ok": ok,
+                   "max_abs_err_fused": float(f"{err:.3e}"), "max_abs_err_reference": float(f"{err_ref:.3e}"),
+                   "bound_2^-8_scale": float(f"{2.0 ** -8 * scale:.3e}"), "ranks_bit_identical": same}
+            if ok:
+                row["us_fused"] = timed(lambda: ops.rowparallel_linear_allreduce(x, w, None, comm))
+                row["us_nccl"] = timed(lambda: reference(x, w))
+                row["speedup"] = round(row["us_nccl"] / row["us_fused"], 2)
+                # rooflines of one call: W streamed once from HBM vs the fp32 partials a rank must push over NVLink
+                wbytes, push = h * kr * 2, n * h * 4 * (world - 1)
+                row["hbm_floor_us"] = round(wbytes / (peaks()[0] * 1e3), 2)
+                row["nvlink_push_bytes"] = push
+                row["nvlink_floor_us_at_770GBps"] = round(push / 770e3, 2)
+            rows.append(row)
+    torch.cuda.synchronize()
+    dist.barrier()
+    rp.release() if False else None
+    return {"parity_ok": all_ok, "world": world, "transport": comm.how, "timeout_latch": rp.poll_error(),
+            "timing": f"CUDA-graph chains of {chain} calls x {iters} replays, max over ranks", "rows": rows}
+
+
+def run_tp_e2e(args, world):
+    """The metric BASELINE.json names beside the op-level one: bench_my decode tok/s of the reference ENGINE at
+    tensor_parallel_size = N (its own spawned ranks, NCCL, scheduler, CUDA graphs), `flash` backend vs `cuda` backend
+    (and `cuda` with the NCCL all-reduce when N > 1), bounded: Qwen3-0.6B random-init, bs 64, input 512, output 128.
+    Runs tools/bench_my_b200.py as a subprocess of rank 0 after the torchrun ranks have released their GPUs."""
+    import signal
+    script = os.path.join(ROOT, "tools", "bench_my_b200.py")
+    env = {k: v for k, v in os.environ.items()
+           if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "ROLE_RANK",
+                        "LOCAL_WORLD_SIZE", "ROLE_WORLD_SIZE", "TORCHELASTIC_RUN_ID", "TORCHELASTIC_RESTART_COUNT",
+                        "TORCHELASTIC_MAX_RESTARTS", "TORCHELASTIC_USE_AGENT_STORE", "TORCH_NCCL_ASYNC_ERROR_HANDLING",
+                        "TORCHELASTIC_ERROR_FILE", "OMP_NUM_THREADS")}
+    arms = [("flash", {}), ("cuda", {})]
+    if world > 1:
+        arms.append(("cuda", {"NVLLM_FUSED_ALLREDUCE": "0"}))
+    out = {"workload": f"reference engine, Qwen3-0.6B random-init, tensor_parallel_size={world}, bs 64, input 512, "
+                       f"output 128, temperature 0, ignore_eos (bench_my protocol, tok/s = bs*out/wall)", "arms": []}
+    deadline = time.time() + args.tp_e2e_timeout
+    for i, (backend, extra) in enumerate(arms):
+        left = deadline - time.time()
+        label = backend + ("+nccl_allreduce" if extra else ("+fused_allreduce" if backend == "cuda" and world > 1 else ""))
+        if left < 45:
+            out["arms"].append({"arm": label, "skipped": "time budget of the tp_e2e leg spent"})
+            continue
+        try:   # a crashed engine leaves its control-plane segment behind (model_runner.py:52)
+            from multiprocessing import shared_memory
+            shm = shared_memory.SharedMemory(name="nanovllm")
+            shm.close()
+            shm.unlink()
+        except Exception:
+            pass
+        res_path = os.path.join(tempfile.gettempdir(), f"nvllm_tp_e2e_{os.getpid()}_{i}.json")
+        cmd = [sys.executable, script, "--attn-backend", backend, "--batch-sizes", "64", "--input-lens", "512",
+               "--output-len", "128", "--tensor-parallel-size", str(world), "--port", str(2400 + 7 * i), "--out", res_path]
+        e = dict(env)
+        e.update(extra)
+        t0 = time.time()
+        proc = subprocess.Popen(cmd, env=e, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                                start_new_session=True)
+        try:
+            log, _ = proc.communicate(timeout=left)
+        except subprocess.TimeoutExpired:
+            try:
+                os.killpg(proc.pid, signal.SIGKILL)
+            except Exception:
+                proc.kill()
+            log, _ = proc.communicate()
+            out["arms"].append({"arm": label, "failed": "timeout", "log_tail": (log or "")[-300:]})
+            continue
+        row = {"arm": label, "wall_s": round(time.time() - t0, 1)}
+        try:
+            with open(res_path) as f:
+                r = json.load(f)["results"][backend]["64x512"]
+            row.update(tok_s=r["tok_s"], ms=r["ms"])
+            os.unlink(res_path)
+        except Exception as ex:
+            row.update(failed=f"rc={proc.returncode} {type(ex).__name__}", log_tail=(log or "")[-400:])
+        out["arms"].append(row)
+    good = {a["arm"]: a["tok_s"] for a in out["arms"] if "tok_s" in a}
+    if "flash" in good:
+        for k2, v in good.items():
+            if k2 != "flash":
+                out[f"{k2}_over_flash"] = round(v / good["flash"], 3)
     return out
 
 

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define NVLLM_ABI_VERSION 1
+#define NVLLM_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define NVLLM_API __attribute__((visibility("default")))
@@ -114,13 +114,24 @@ NVLLM_API int nvllm_store_kvcache(const void* key, int64_t key_row_stride,
  *   k_cache/v_cache [num_blocks, block_size, num_kv_heads, head_dim]:
  *       cache_block_stride between blocks, cache_token_stride between tokens,
  *       head stride head_dim, unit inner stride.
- *   num_splits >= 1: split-KV (flash-decoding).  Each split takes an equal
- *   share of the LIVE ctx_b (not of the table width).  num_splits > 1 needs a
- *   workspace of nvllm_paged_decode_workspace_bytes(); the last split CTA
- *   of each (sequence, kv head) merges the partials inside the same launch.
- *   The workspace must be ZERO-FILLED ONCE before its first use (its first 64 KiB
- *   hold self-resetting arrival counters, then the partials) and must not be
- *   shared by launches that may run concurrently.
+ *   num_splits >= 1: split-KV grid (num_splits, num_kv_heads, bs), at most 128
+ *   splits.  Each split takes an equal share of the LIVE ctx_b (not of the
+ *   table width); the last split CTA of each (sequence, kv head) to arrive
+ *   merges the partials inside the same launch.  This is what
+ *   nvllm_paged_decode_plan returns by default.
+ *   num_splits <= 0: BALANCED persistent grid (opt-in; measured slower than
+ *   the split-KV grid on B200): -num_splits CTAs, 0 =
+ *   fill the SMs (two 4-warp CTAs per SM for G <= 4, else one 8-warp CTA; at
+ *   most 512).  The kernel concatenates the 16-token K/V slices of all
+ *   (sequence, kv head) items, reads the LIVE context_lens and gives every
+ *   CTA an equal contiguous share; a CTA whose share cuts an item writes one
+ *   fp32 partial and the CTA completing the item merges them in the same
+ *   launch.  Needs bs * num_kv_heads <= 16384 and table_stride * block_size
+ *   <= 2^24 (else NVLLM_ERR_UNSUPPORTED).
+ *   Every form but num_splits == 1 needs a workspace of
+ *   nvllm_paged_decode_workspace_bytes(), which must be ZERO-FILLED ONCE before
+ *   its first use (its first 64 KiB hold self-resetting arrival counters, then
+ *   the partials) and must not be shared by launches that may run concurrently.
  *   Supported: head_dim == 128, G in {1,2,4,8}, block_size % 32 == 0.
  * ---------------------------------------------------------------------- */
 NVLLM_API int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride,
@@ -133,15 +144,20 @@ NVLLM_API int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride,
                        int32_t num_splits, void* workspace,
                        size_t workspace_bytes, void* stream);
 
-/* Bytes of split-KV workspace for the given geometry (0 when num_splits==1). */
+/* Bytes of workspace for the given geometry: 0 when num_splits == 1; for
+ * num_splits <= 0 (balanced grid) it depends on the CTA count only. */
 NVLLM_API size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads,
                                           int32_t head_dim, int32_t num_splits);
 
 /* Host-side split heuristic (pure function, no CUDA calls besides an SM-count
  * query when sm_count <= 0): picks num_splits from the launch-time-known
  * geometry only — max_ctx is the table width * block_size under CUDA graphs.
- * Returns the split count (>= 1). */
-NVLLM_API int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads,
+ * Returns a split count >= 1: 1 once the (sequence, kv head) items cover ~85 % of
+ * the SMs, else about one CTA per SM (<= 64 splits, >= 256 tokens per split, a
+ * power of two when that keeps >= 3/4 of the CTAs).  NVLLM_DECODE_PLAN=balanced
+ * in the environment makes it return 0 (the balanced persistent grid) wherever
+ * that kernel applies, for A/B runs. */
+NVLLM_API int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_q_heads, int32_t num_kv_heads,
                                 int32_t max_ctx, int32_t sm_count);
 
 /* Tuning hook: selects the decode tile variant (warps/stages/chunk) used by
@@ -149,6 +165,10 @@ NVLLM_API int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads,
  * default.  Returns NVLLM_ERR_BAD_ARG for an unknown id. */
 NVLLM_API int nvllm_paged_decode_set_variant(int32_t variant);
 NVLLM_API int32_t nvllm_paged_decode_num_variants(void);
+/* Tuning hooks of the balanced grid: 16-token chunks of one kv head a CTA owns at
+ * least (fewer CTAs take part when the live work is small; <= 0 = default), and
+ * warps per CTA (4 = two CTAs per SM, needs G <= 4; 8 = one CTA per SM; else automatic). */
+NVLLM_API int nvllm_paged_decode_set_tuning(int32_t min_chunks_per_cta, int32_t warps_per_cta);
 
 /* ------------------------------------------------------------------------
  * (3) varlen causal prefill with optional paged prefix (prefix cache).

@@ -22,6 +22,11 @@ extern "C" {
  * behind them (>= 147456 bytes in all). */
 NVLLM_API void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr);
 
+/* tools/trace_decode.py: when non-NULL, thread 0 of every CTA of the fixed-grid paged-decode kernel stamps
+ * %globaltimer (ns) at six protocol points into buffer[cta * 8 + k]: 0 entry, 1 first copies issued, 2 first chunk
+ * landed, 3 main loop done, 4 partial published, 5 exit (combining CTA only); cta = (b * Hkv + kvh) * S + split. */
+NVLLM_API int nvllm_paged_decode_set_trace(void* device_buffer);
+
 /* tools/membench.py: streams `bytes` of `buf` with contiguous warp reads (pattern 0) or with the
  * decode kernel's 256-byte-row / token-stride access shape (pattern 1, hkv heads). */
 NVLLM_API int nvllm_debug_stream_read(const void* buf, int64_t bytes, int32_t pattern,

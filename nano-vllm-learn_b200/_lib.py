@@ -24,9 +24,10 @@ SIGNATURES = {
                                    c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                    c_float, c_int32, c_void_p, c_size_t, c_void_p]),
     "nvllm_paged_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
-    "nvllm_paged_decode_plan": (c_int32, [c_int32, c_int32, c_int32, c_int32]),
+    "nvllm_paged_decode_plan": (c_int32, [c_int32, c_int32, c_int32, c_int32, c_int32]),
     "nvllm_paged_decode_set_variant": (c_int, [c_int32]),
     "nvllm_paged_decode_num_variants": (c_int32, []),
+    "nvllm_paged_decode_set_tuning": (c_int, [c_int32, c_int32]),
     "nvllm_varlen_prefill": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64,
                                      c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p,
                                      c_int64, c_int32, c_int32, c_int32, c_int32, c_float, c_void_p]),
@@ -63,10 +64,11 @@ SIGNATURES = {
 # include/nvllm_tools.h (lib/libnvllm_tools.so only; tools/*.py call load_tools())
 TOOLS_SIGNATURES = {
     "nvllm_varlen_prefill_set_debug_buffer": (None, [c_void_p]),
+    "nvllm_paged_decode_set_trace": (c_int, [c_void_p]),
     "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
 }
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 _LIB = None
 
 

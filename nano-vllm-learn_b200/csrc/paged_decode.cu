@@ -18,7 +18,10 @@
 //  * warps merge their (m, l, O) in shared memory once; with num_splits > 1 the CTA writes a
 //    normalised partial + log2-sum-exp, and the last split CTA of a (sequence, kv head) to arrive
 //    (atomic counter in the workspace, self-resetting) merges the splits — no second launch.
+#include <cstdlib>
+
 #include "common.cuh"
+#include "paged_decode_params.cuh"
 
 namespace nvllm {
 
@@ -39,6 +42,7 @@ struct DecodeParams {
   int32_t num_q_heads;
   int32_t group;       // G = Hq / Hkv
   int32_t block_size;
+  int32_t block_shift; // log2(block_size) when it is a power of two, else -1
   int32_t num_splits;
   float scale_log2;    // softmax scale * log2(e)
 };
@@ -57,6 +61,23 @@ struct DecodeCfg {
   static constexpr int kSmemBytes = kPipeBytes > kMergeBytes ? kPipeBytes : kMergeBytes;
 };
 
+#ifdef NVLLM_TOOLS_BUILD
+// tools/trace_decode.py: thread 0 of every CTA stamps %globaltimer at the protocol points below into
+// trace[cta * 8 + k] (k: 0 entry, 1 first copies issued, 2 first chunk landed, 3 main loop done, 4 partial published,
+// 5 exit; cta = (b * Hkv + kvh) * S + split).
+static __device__ unsigned long long* g_decode_trace = nullptr;
+#define NVLLM_TRACE(k)                                                                                        \
+  do {                                                                                                        \
+    if (g_decode_trace != nullptr && threadIdx.x == 0) {                                                      \
+      unsigned long long t_;                                                                                  \
+      asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t_));                                                \
+      g_decode_trace[((static_cast<size_t>(blockIdx.z) * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (k)] = t_; \
+    }                                                                                                         \
+  } while (0)
+#else
+#define NVLLM_TRACE(k) do { } while (0)
+#endif
+
 template <class Cfg>
 __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const DecodeParams p) {
   constexpr int CHUNK = Cfg::kChunk;
@@ -67,6 +88,7 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   constexpr int PIECES = CHUNK * 16 / 32;  // 16-byte pieces per lane per tensor per chunk
 
   extern __shared__ __align__(128) unsigned char smem[];
+  NVLLM_TRACE(0);
 
   const int split = blockIdx.x;
   const int kvh = blockIdx.y;
@@ -113,27 +135,48 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   const int col16 = lane & 15;
   const int tok_lo = lane >> 4;
 
+  // token -> (page slot, row in page): block sizes are powers of two in practice (256); shift/mask instead of a divide
+  const int bshift = p.block_shift;
+  // Per-lane copy geometry, fixed for the whole kernel: piece j copies token 2j + tok_lo; source addresses advance by a
+  // constant byte step, destinations are swizzled offsets whose XOR only depends on (2j + tok_lo) & 7, i.e. on j & 3.
+  const char* const k_bytes = reinterpret_cast<const char*>(p.k_cache);
+  const int64_t kv_delta = reinterpret_cast<const char*>(p.v_cache) - k_bytes;
+  const int64_t step_bytes = 4 * p.token_stride;                       // two tokens further, bf16
+  const int64_t lane_bytes = 2 * (static_cast<int64_t>(tok_lo) * p.token_stride + col16 * 8 + head_off);
+  uint32_t dsw[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) dsw[j] = swz_off(j * 2 + tok_lo, col16);
   auto issue = [&](int i, int page) {
     const int chunk = c_begin + warp + i * WARPS;
     const int t0 = chunk * CHUNK;
-    const int in_page = t0 % p.block_size;
-    const int64_t base = static_cast<int64_t>(page) * p.block_stride + head_off + col16 * 8;
+    const int in_page = bshift >= 0 ? (t0 & (p.block_size - 1)) : (t0 % p.block_size);
+    const char* kp = k_bytes + lane_bytes +
+                     2 * (static_cast<int64_t>(page) * p.block_stride + static_cast<int64_t>(in_page) * p.token_stride);
     const uint32_t sk = my_smem_u32 + (i % STAGES) * Cfg::kStageBytes;
     const uint32_t sv = sk + Cfg::kTileBytes;
+    if (t0 + CHUNK <= ctx) {   // full chunk (all but the last one of the sequence): no per-piece predicate
 #pragma unroll
-    for (int j = 0; j < PIECES; ++j) {
-      const int tok = j * 2 + tok_lo;
-      const uint32_t nbytes = (t0 + tok < ctx) ? 16u : 0u;
-      const int64_t off = base + static_cast<int64_t>(in_page + tok) * p.token_stride;
-      const uint32_t d = swz_off(tok, col16);
-      cp_async16(sk + d, p.k_cache + off, nbytes);
-      cp_async16(sv + d, p.v_cache + off, nbytes);
+      for (int j = 0; j < PIECES; ++j) {
+        const uint32_t d = dsw[j & 3] + (j >> 2) * (8 * kRowBytes);
+        cp_async16_full(sk + d, kp);
+        cp_async16_full(sv + d, kp + kv_delta);
+        kp += step_bytes;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < PIECES; ++j) {
+        const uint32_t nbytes = (t0 + j * 2 + tok_lo < ctx) ? 16u : 0u;   // beyond the context: zero-fill
+        const uint32_t d = dsw[j & 3] + (j >> 2) * (8 * kRowBytes);
+        cp_async16(sk + d, kp, nbytes);
+        cp_async16(sv + d, kp + kv_delta, nbytes);
+        kp += step_bytes;
+      }
     }
   };
   auto page_of = [&](int i) -> int {
     if (i >= n_my) return 0;
-    const int chunk = c_begin + warp + i * WARPS;
-    return __ldg(table + (chunk * CHUNK) / p.block_size);
+    const int t0 = (c_begin + warp + i * WARPS) * CHUNK;
+    return __ldg(table + (bshift >= 0 ? (t0 >> bshift) : (t0 / p.block_size)));
   };
 
   // ---- prologue: fill STAGES-1 stages -----------------------------------------------------
@@ -146,6 +189,7 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
     cp_async_commit();
   }
 
+  NVLLM_TRACE(1);
   for (int i = 0; i < n_my; ++i) {
     {
       const int nxt = i + STAGES - 1;
@@ -156,6 +200,7 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
     }
     cp_async_wait<STAGES - 1>();
     __syncwarp();
+    if (i == 0) NVLLM_TRACE(2);
 
     const uint32_t sk = my_smem_u32 + (i % STAGES) * Cfg::kStageBytes;
     const uint32_t sv = sk + Cfg::kTileBytes;
@@ -177,20 +222,21 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
     }
 
     // ---- online softmax on rows 0..7 (this lane: row lane>>2, tokens nt*8 + (lane&3)*2 + {0,1})
+    if (t0 + CHUNK > ctx) {   // only the last chunk of the sequence has tokens beyond the context
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const int t = t0 + nt * 8 + (lane & 3) * 2;
+        if (t >= ctx) s[nt][0] = -INFINITY;
+        if (t + 1 >= ctx) s[nt][1] = -INFINITY;
+      }
+    }
     float mx = -INFINITY;
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-      const int t = t0 + nt * 8 + (lane & 3) * 2;
-      if (t >= ctx) s[nt][0] = -INFINITY;
-      if (t + 1 >= ctx) s[nt][1] = -INFINITY;
-      mx = fmaxf(mx, fmaxf(s[nt][0], s[nt][1]));
-    }
+    for (int nt = 0; nt < NT; ++nt) mx = fmaxf(mx, fmaxf(s[nt][0], s[nt][1]));
     mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
     mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
     const float m_new = fmaxf(m_run, mx);  // finite: every chunk holds at least one live token
-    const float alpha = fast_exp2((m_run - m_new) * p.scale_log2);
     const float m_scaled = m_new * p.scale_log2;
-    m_run = m_new;
     float psum = 0.f;
     uint32_t pa0[KS], pa2[KS];
 #pragma unroll
@@ -203,12 +249,18 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
       pa0[ks] = pack_bf16x2(p00, p01);
       pa2[ks] = pack_bf16x2(p10, p11);
     }
-    l_run = l_run * alpha + psum;
+    // the running max settles after a few chunks: rescale O only when some row's max actually moved
+    if (__any_sync(0xffffffffu, m_new != m_run)) {
+      const float alpha = fast_exp2((m_run - m_new) * p.scale_log2);
+      l_run *= alpha;
 #pragma unroll
-    for (int i2 = 0; i2 < 16; ++i2) {
-      o[i2][0] *= alpha;
-      o[i2][1] *= alpha;
+      for (int i2 = 0; i2 < 16; ++i2) {
+        o[i2][0] *= alpha;
+        o[i2][1] *= alpha;
+      }
+      m_run = m_new;
     }
+    l_run += psum;
 
     // ---- O += P . V  (16 x 128) ------------------------------------------------------------
 #pragma unroll
@@ -225,6 +277,7 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
     __syncwarp();
   }
   cp_async_wait<0>();
+  NVLLM_TRACE(3);
 
   // ---- merge the warps of this CTA ---------------------------------------------------------
   l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
@@ -274,37 +327,110 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   // ---- fused combine: the LAST split CTA of this (sequence, kv head) to arrive merges all partials.
   // out = sum_s 2^(lse_s - L) O_s / sum_s 2^(lse_s - L).  Saves the separate combine launch (5-6 us).
   __shared__ int s_is_last;
-  __threadfence();   // partials of this thread are visible device-wide before the arrival below
-  __syncthreads();
+  __syncthreads();   // every thread's partial stores happen-before thread 0's release below (CTA barrier + cumulativity)
   if (threadIdx.x == 0) {
     int32_t* cnt = p.counters + b * gridDim.y + kvh;
-    const int old = atomicAdd(cnt, 1);
+    int old;
+    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;\n" : "=r"(old) : "l"(cnt) : "memory");
     s_is_last = (old == p.num_splits - 1);
     if (s_is_last) *cnt = 0;   // self-resetting: the next launch (or graph replay) starts from zero
   }
-  __syncthreads();
+  __syncthreads();   // ... and thread 0's acquire happens-before every thread's partial loads
+  NVLLM_TRACE(4);
   if (!s_is_last) return;
-  __threadfence();   // acquire side: order the partial reads after the counter observation
-  for (int idx = threadIdx.x; idx < G * kHeadDim; idx += WARPS * 32) {
-    const int row = idx >> 7;
-    const int d = idx & (kHeadDim - 1);
-    const int64_t base = (static_cast<int64_t>(b) * p.num_q_heads + kvh * G + row) * p.num_splits;
-    const float* lse = p.part_lse + base;
-    float L = -INFINITY;
-    for (int sp = 0; sp < p.num_splits; ++sp) L = fmaxf(L, __ldcg(lse + sp));
-    float num = 0.f, den = 0.f;
-    if (L > -INFINITY) {
-      const float* po = p.part_o + base * kHeadDim + d;
+  // All partial reads are issued with as much memory-level parallelism as the CTA has: thread (group g, row r, float4
+  // column c4) owns every `groups`-th split; its first kBatch partial loads are in flight BEFORE the log2-sum-exps are
+  // fetched to shared memory, so the whole combine costs about one L2 round trip.  (The pipeline rings are idle by now.)
+  {
+    constexpr int NTHR = WARPS * 32;
+    constexpr int kBatch = 16;
+    const int S = p.num_splits;
+    float* const s_lse = reinterpret_cast<float*>(smem);                    // [G][S], S <= 128
+    float4* const s_acc = reinterpret_cast<float4*>(smem + 8 * 128 * 4);    // [groups][G * 32]
+    float* const s_den = reinterpret_cast<float*>(smem + 8 * 128 * 4 + NTHR * 16);
+    const int64_t row0 = static_cast<int64_t>(b) * p.num_q_heads + kvh * G;
+    const int cols = G * 32;
+    const int groups = NTHR / cols;     // >= 1 unless a 2-warp variant meets G = 8
+    if (groups >= 1) {
+      const int g = threadIdx.x / cols, j = threadIdx.x % cols, r = j >> 5, c4 = j & 31;
+      const bool mine = g < groups;
+      const float4* po = reinterpret_cast<const float4*>(p.part_o + (row0 + r) * S * kHeadDim) + c4;
+      float4 v[kBatch];
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u) {
+        const int sp = g + u * groups;
+        v[u] = (mine && sp < S) ? __ldcg(po + static_cast<int64_t>(sp) * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      for (int i = threadIdx.x; i < G * S; i += NTHR) s_lse[i] = __ldcg(p.part_lse + (row0 + i / S) * S + i % S);
+      __syncthreads();
+      if (mine) {
+        float L = -INFINITY;
+        for (int sp = 0; sp < S; ++sp) L = fmaxf(L, s_lse[r * S + sp]);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        float den = 0.f;
+        if (L > -INFINITY) {   // empty splits hold zeros and -inf: weight 0
+#pragma unroll
+          for (int u = 0; u < kBatch; ++u) {
+            const int sp = g + u * groups;
+            const float w = sp < S ? fast_exp2(s_lse[r * S + sp] - L) : 0.f;
+            acc.x += w * v[u].x; acc.y += w * v[u].y; acc.z += w * v[u].z; acc.w += w * v[u].w;
+            den += w;
+          }
+          for (int sp0 = g + kBatch * groups; sp0 < S; sp0 += kBatch * groups) {
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+              const int sp = sp0 + u * groups;
+              v[u] = sp < S ? __ldcg(po + static_cast<int64_t>(sp) * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < kBatch; ++u) {
+              const int sp = sp0 + u * groups;
+              const float w = sp < S ? fast_exp2(s_lse[r * S + sp] - L) : 0.f;
+              acc.x += w * v[u].x; acc.y += w * v[u].y; acc.z += w * v[u].z; acc.w += w * v[u].w;
+              den += w;
+            }
+          }
+        }
+        s_acc[g * cols + j] = acc;
+        s_den[g * cols + j] = den;
+      }
+      __syncthreads();
+      if (threadIdx.x < cols) {
+        float4 acc = s_acc[threadIdx.x];
+        float den = s_den[threadIdx.x];
+        for (int gg = 1; gg < groups; ++gg) {
+          const float4 t = s_acc[gg * cols + threadIdx.x];
+          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+          den += s_den[gg * cols + threadIdx.x];
+        }
+        const float inv = den > 0.f ? 1.f / den : 0.f;
+        uint2 pk;
+        pk.x = pack_bf16x2(acc.x * inv, acc.y * inv);
+        pk.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+        *reinterpret_cast<uint2*>(p.out + (row0 + r) * kHeadDim + c4 * 4) = pk;
+      }
+    } else {   // fewer threads than float4 columns (2-warp variants with G = 8): plain strided loop
+      for (int i = threadIdx.x; i < G * S; i += NTHR) s_lse[i] = __ldcg(p.part_lse + (row0 + i / S) * S + i % S);
+      __syncthreads();
+      for (int idx = threadIdx.x; idx < G * kHeadDim; idx += NTHR) {
+        const int row = idx >> 7, d = idx & (kHeadDim - 1);
+        float L = -INFINITY;
+        for (int sp = 0; sp < S; ++sp) L = fmaxf(L, s_lse[row * S + sp]);
+        float num = 0.f, den = 0.f;
+        if (L > -INFINITY) {
+          const float* po = p.part_o + (row0 + row) * S * kHeadDim + d;
 #pragma unroll 4
-      for (int sp = 0; sp < p.num_splits; ++sp) {
-        const float w = fast_exp2(__ldcg(lse + sp) - L);
-        num += w * __ldcg(po + static_cast<int64_t>(sp) * kHeadDim);
-        den += w;
+          for (int sp = 0; sp < S; ++sp) {
+            const float w = fast_exp2(s_lse[row * S + sp] - L);
+            num += w * __ldcg(po + static_cast<int64_t>(sp) * kHeadDim);
+            den += w;
+          }
+        }
+        p.out[(row0 + row) * kHeadDim + d] = __float2bfloat16_rn(den > 0.f ? num / den : 0.f);
       }
     }
-    p.out[(static_cast<int64_t>(b) * p.num_q_heads + kvh * G + row) * kHeadDim + d] =
-        __float2bfloat16_rn(den > 0.f ? num / den : 0.f);
   }
+  NVLLM_TRACE(5);
 }
 
 // ---- variants -------------------------------------------------------------------------------
@@ -338,33 +464,56 @@ static cudaError_t launch_decode(const DecodeParams& p, int bs, int hkv, cudaStr
 
 }  // namespace nvllm
 
+#ifdef NVLLM_TOOLS_BUILD
+#include "../../include/nvllm_tools.h"
+extern "C" int nvllm_paged_decode_set_trace(void* device_buffer) {
+  unsigned long long* p = static_cast<unsigned long long*>(device_buffer);
+  return nvllm::record_cuda_error(cudaMemcpyToSymbol(nvllm::g_decode_trace, &p, sizeof(p)));
+}
+#endif
+
 extern "C" {
 
 size_t nvllm_paged_decode_workspace_bytes(int32_t bs, int32_t num_q_heads, int32_t head_dim, int32_t num_splits) {
-  if (bs <= 0 || num_q_heads <= 0 || head_dim <= 0 || num_splits <= 1) return 0;
+  if (bs <= 0 || num_q_heads <= 0 || head_dim <= 0 || num_splits == 1) return 0;
+  if (num_splits <= 0) return nvllm::balanced_decode_workspace_bytes(-num_splits);   // balanced grid: batch-independent
   const size_t rows = static_cast<size_t>(bs) * num_q_heads * num_splits;
   // [fixed 64 KiB of per-(sequence, kv head) arrival counters] | partial O | partial LSE.  The counter area
   // sits at a geometry-independent place so one zero-filled workspace can serve calls of any shape.
   return nvllm::kCounterBytes + rows * head_dim * sizeof(float) + rows * sizeof(float);
 }
 
-int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ctx, int32_t sm_count) {
-  if (bs <= 0 || num_kv_heads <= 0 || max_ctx <= 0) return 1;
+int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_q_heads, int32_t num_kv_heads, int32_t max_ctx,
+                                int32_t sm_count) {
+  if (bs <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || max_ctx <= 0) return 1;
   if (sm_count <= 0) sm_count = nvllm::sm_count_cached();
-  // HBM-bound kernel: what matters is enough CTAs in flight to saturate HBM (about two resident 4-warp
-  // CTAs per SM), not wave quantisation — measured on B200 (profiles/r01_decode_sweep_*.jsonl), one split
-  // is fastest as soon as (sequence, kv-head) items cover ~85 % of the SMs, because every extra split
-  // pays the partial write + combine pass.  Below that, split up to one CTA per SM, but keep >= 256 tokens
-  // of the (launch-time upper bound of the) context per split.
+  // Default: the per-(sequence, kv head, split) grid.  NVLLM_DECODE_PLAN=balanced returns 0 = the persistent balanced grid
+  // (paged_decode_balanced.cu), kept as an opt-in: measured on B200 it loses to the fixed grid on every shape of the
+  // round-2 sweeps (profiles/r02_decode_sweep.md) -- the SMs stream at different HBM rates, so equal static ranges finish
+  // 15-20 % apart, and its segment bookkeeping costs 8-10 us of fixed overhead.
+  const char* plan_env = getenv("NVLLM_DECODE_PLAN");   // read per call: callers cache plans, tests flip it
   const int64_t items = static_cast<int64_t>(bs) * num_kv_heads;
+  if (plan_env && plan_env[0] == 'b' && bs <= nvllm::kBalancedMaxBatch &&
+      num_q_heads <= nvllm::kBalancedMaxGroup * num_kv_heads && max_ctx <= nvllm::kBalancedMaxContext &&
+      items * static_cast<int64_t>(sizeof(int32_t)) <= static_cast<int64_t>(nvllm::kCounterBytes) &&
+      items * ((max_ctx + 15) / 16) < (int64_t(1) << 31))
+    return 0;
+  // HBM-bound kernel: what matters is enough CTAs in flight to saturate HBM, not wave quantisation -- measured on B200
+  // (profiles/r01_decode_sweep_*.jsonl, profiles/r02_decode_sweep.md), one split is fastest as soon as (sequence,
+  // kv-head) items cover ~85 % of the SMs, because every extra split pays the partial write + combine pass.
   if (items * 100 >= static_cast<int64_t>(sm_count) * 85) return 1;
-  // One wave of one 8-warp CTA per SM (floor, not ceil): a few CTAs spilling into a second wave cannot
-  // saturate HBM on their own and double the time (bs=4 ctx=32768: 10 splits 137 us, 8 splits 105 us), and
-  // fewer, fatter splits mean fewer partials for the combine pass.
+  // Below that: one wave of one 8-warp CTA per SM (floor, not ceil: a few CTAs spilling into a second wave cannot
+  // saturate HBM on their own), at most 64 splits (past that the combine of the partials costs more than the extra
+  // CTAs stream), >= 256 tokens of the launch-time context bound per split, and a power of two when that keeps >= 3/4
+  // of the CTAs: contexts are block multiples, so a power-of-two split count hands every warp the same number of
+  // chunks (ctx 32768, 8 items: 16 splits 27.2 us, 18 splits 28.3 us).
   int64_t s = static_cast<int64_t>(sm_count) / items;
   const int64_t by_len = max_ctx / 256 > 1 ? max_ctx / 256 : 1;
   if (s > by_len) s = by_len;
-  if (s > 128) s = 128;
+  if (s > 64) s = 64;
+  int64_t pow2 = 1;
+  while (pow2 * 2 <= s) pow2 *= 2;
+  if (pow2 * 4 >= s * 3) s = pow2;
   const int best = static_cast<int>(s < 1 ? 1 : s);
   return best;
 }
@@ -372,6 +521,11 @@ int32_t nvllm_paged_decode_plan(int32_t bs, int32_t num_kv_heads, int32_t max_ct
 int nvllm_paged_decode_set_variant(int32_t variant) {
   if (variant < -1 || variant >= nvllm::kNumVariants) return NVLLM_ERR_BAD_ARG;
   nvllm::g_variant = variant;
+  return NVLLM_OK;
+}
+int nvllm_paged_decode_set_tuning(int32_t min_chunks_per_cta, int32_t warps_per_cta) {
+  nvllm::balanced_decode_set_min_chunks(min_chunks_per_cta);
+  nvllm::balanced_decode_set_warps(warps_per_cta);
   return NVLLM_OK;
 }
 int32_t nvllm_paged_decode_num_variants(void) { return nvllm::kNumVariants; }
@@ -382,20 +536,55 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
                        int32_t num_kv_heads, int32_t head_dim, int32_t block_size, float scale, int32_t num_splits,
                        void* workspace, size_t workspace_bytes, void* stream) {
   using namespace nvllm;
-  if (bs < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || block_size <= 0 || num_splits < 1)
+  if (bs < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || block_size <= 0 || num_splits < -512)
     return NVLLM_ERR_BAD_ARG;
   if (bs == 0) return NVLLM_OK;
   if (!out || !q || !k_cache || !v_cache || !block_tables || !context_lens) return NVLLM_ERR_BAD_ARG;
   if (head_dim != kHeadDim || num_q_heads % num_kv_heads != 0 || block_size % 32 != 0) return NVLLM_ERR_UNSUPPORTED;
   const int G = num_q_heads / num_kv_heads;
   if (G > 8) return NVLLM_ERR_UNSUPPORTED;
-  if (bs > 65535 || num_kv_heads > 65535) return NVLLM_ERR_UNSUPPORTED;
+  if (bs > 65535 || num_kv_heads > 65535 || num_splits > 128) return NVLLM_ERR_UNSUPPORTED;
   if (q_row_stride < static_cast<int64_t>(num_q_heads) * head_dim || table_stride < 0) return NVLLM_ERR_BAD_ARG;
   if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache) || (q_row_stride & 7) ||
       (cache_block_stride & 7) || (cache_token_stride & 7))
     return NVLLM_ERR_ALIGNMENT;
   const size_t need = nvllm_paged_decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits);
-  if (num_splits > 1 && (!workspace || workspace_bytes < need || !aligned16(workspace))) return NVLLM_ERR_WORKSPACE;
+  if (num_splits != 1 && (!workspace || workspace_bytes < need || !aligned16(workspace))) return NVLLM_ERR_WORKSPACE;
+
+  if (num_splits <= 0) {
+    // balanced persistent grid: -num_splits CTAs (0 = one per SM); the chunk index space must fit 31 bits
+    if (static_cast<size_t>(bs) * num_kv_heads * sizeof(int32_t) > kCounterBytes) return NVLLM_ERR_UNSUPPORTED;
+    if (bs > kBalancedMaxBatch || G > kBalancedMaxGroup || table_stride * block_size > kBalancedMaxContext)
+      return NVLLM_ERR_UNSUPPORTED;
+    if (static_cast<int64_t>(bs) * num_kv_heads * ((table_stride > 0 ? table_stride : 1) * block_size / 16 + 1) >=
+        (int64_t(1) << 31))
+      return NVLLM_ERR_UNSUPPORTED;
+    BalancedDecodeParams bp;
+    bp.q = static_cast<const __nv_bfloat16*>(q);
+    bp.q_row_stride = q_row_stride;
+    bp.k_cache = static_cast<const __nv_bfloat16*>(k_cache);
+    bp.v_cache = static_cast<const __nv_bfloat16*>(v_cache);
+    bp.block_stride = cache_block_stride;
+    bp.token_stride = cache_token_stride;
+    bp.block_tables = block_tables;
+    bp.table_stride = table_stride;
+    bp.context_lens = context_lens;
+    bp.out = static_cast<__nv_bfloat16*>(out);
+    bp.part_o = nullptr;
+    bp.part_lse = nullptr;
+    bp.counters = nullptr;
+    bp.bs = bs;
+    bp.num_q_heads = num_q_heads;
+    bp.num_kv_heads = num_kv_heads;
+    bp.group = G;
+    bp.block_size = block_size;
+    bp.block_shift = -1;
+    bp.min_chunks_per_cta = 0;
+    bp.scale_log2 = scale * kLog2e;
+    const cudaError_t be = launch_balanced_decode(bp, -num_splits, workspace, static_cast<cudaStream_t>(stream));
+    note_launch();
+    return record_cuda_error(be);
+  }
 
   DecodeParams p;
   p.q = static_cast<const __nv_bfloat16*>(q);
@@ -421,6 +610,9 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
   p.num_q_heads = num_q_heads;
   p.group = G;
   p.block_size = block_size;
+  p.block_shift = -1;
+  for (int sh = 0; sh < 31; ++sh)
+    if ((1 << sh) == block_size) p.block_shift = sh;
   p.num_splits = num_splits;
   p.scale_log2 = scale * kLog2e;
 

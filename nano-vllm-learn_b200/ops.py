@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 
-_PLAN_CACHE: dict[tuple[int, int, int], int] = {}
+_PLAN_CACHE: dict[tuple[int, int, int, int], int] = {}
 # Split-KV workspace, one per device, shared by all layers (they run back to back on one stream).  It is
 # zero-filled once (the kernel's arrival counters reset themselves) and only ever grows; superseded buffers
 # stay referenced because captured CUDA graphs may still point at them.
@@ -142,11 +142,12 @@ def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: tor
     return q, k
 
 
-def plan_num_splits(bs: int, num_kv_heads: int, max_ctx: int) -> int:
-    key = (bs, num_kv_heads, max_ctx)
+def plan_num_splits(bs: int, num_q_heads: int, num_kv_heads: int, max_ctx: int) -> int:
+    """Split count (>= 1) of the split-KV decode grid; 0 (balanced persistent grid) only under NVLLM_DECODE_PLAN=balanced."""
+    key = (bs, num_q_heads, num_kv_heads, max_ctx)
     s = _PLAN_CACHE.get(key)
     if s is None:
-        s = int(_lib.load().nvllm_paged_decode_plan(bs, num_kv_heads, max_ctx, 0))
+        s = int(_lib.load().nvllm_paged_decode_plan(bs, num_q_heads, num_kv_heads, max_ctx, 0))
         _PLAN_CACHE[key] = s
     return s
 
@@ -158,12 +159,13 @@ def decode_workspace_bytes(bs: int, num_q_heads: int, head_dim: int, num_splits:
 def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                             cache_seqlens: torch.Tensor, block_table: torch.Tensor,
                             softmax_scale: Optional[float] = None, causal: bool = True,
-                            num_splits: int = 0, out: Optional[torch.Tensor] = None,
+                            num_splits: Optional[int] = None, out: Optional[torch.Tensor] = None,
                             workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Paged decode.  q [bs, 1, Hq, D] (or [bs, Hq, D]); returns the same shape.
 
     `causal` is accepted for signature parity; with one query token the bottom-right causal mask is
-    a no-op.  num_splits=0 lets the library plan from (bs, Hkv, table width) only.
+    a no-op.  num_splits=None lets the library plan from (bs, Hkv, table width) only; >= 1 is the split-KV grid,
+    0 (or -P) the opt-in balanced persistent grid with one CTA per SM (or P CTAs).
     """
     lib = _lib.load()
     _require_cuda(q, k_cache, v_cache, cache_seqlens, block_table)
@@ -183,8 +185,8 @@ def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: tor
     assert block_table.dtype == torch.int32 and block_table.stride(-1) == 1 and block_table.size(0) == bs
     if softmax_scale is None:
         softmax_scale = head_dim ** -0.5
-    if num_splits <= 0:
-        num_splits = plan_num_splits(bs, num_kv_heads, block_table.size(1) * block_size)
+    if num_splits is None:
+        num_splits = plan_num_splits(bs, num_q_heads, num_kv_heads, block_table.size(1) * block_size)
     if out is None:
         out = torch.empty((bs, num_q_heads, head_dim), dtype=q.dtype, device=q.device)
     ws_bytes = decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits)

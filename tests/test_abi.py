@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_abi_version_and_strings(lib):
-    assert lib.nvllm_abi_version() == 1
+    assert lib.nvllm_abi_version() == 2
     assert lib.nvllm_status_string(0) == b"ok"
     for s in range(1, 6):
         assert lib.nvllm_status_string(s) not in (b"ok", b"unknown status")
@@ -54,7 +54,8 @@ def test_argument_validation_without_gpu(lib):
     assert dec(hq=24, hkv=1) == 2            # G = 24 > 8
     assert dec(hq=10, hkv=4) == 2            # not divisible
     assert dec(bsz=100) == 2
-    assert dec(splits=0) == 1
+    assert dec(splits=-513) == 1             # balanced grid: at most 512 CTAs
+    assert dec(splits=0) == 5                # balanced grid: workspace required
     assert dec(splits=4) == 5                # workspace required
     assert lib.nvllm_paged_decode_workspace_bytes(2, 16, 128, 1) == 0
     assert lib.nvllm_paged_decode_workspace_bytes(2, 16, 128, 4) == 65536 + 2 * 16 * 4 * (128 * 4 + 4)
@@ -72,15 +73,31 @@ def test_argument_validation_without_gpu(lib):
     assert lib.nvllm_paged_decode_num_variants() >= 1
 
 
-def test_plan_is_sane(lib):
+def test_plan_is_sane(lib, monkeypatch):
+    monkeypatch.delenv("NVLLM_DECODE_PLAN", raising=False)
     for bs, hkv, ctx in [(1, 8, 512), (16, 8, 4096), (64, 8, 4096), (128, 8, 4096), (128, 1, 4096), (1, 1, 40960),
-                         (4, 8, 40960)]:
-        s = lib.nvllm_paged_decode_plan(bs, hkv, ctx, 148)
-        assert 1 <= s <= 128
-        assert ctx // s >= 64 or s == 1
-    # tiny grids must be split, saturated grids must not be split much
-    assert lib.nvllm_paged_decode_plan(1, 1, 40960, 148) >= 32
-    assert lib.nvllm_paged_decode_plan(512, 8, 4096, 148) <= 2
+                         (4, 8, 40960), (5, 1, 32768), (3, 8, 8192)]:
+        s = lib.nvllm_paged_decode_plan(bs, 2 * hkv, hkv, ctx, 148)
+        assert 1 <= s <= 64
+        assert ctx // s >= 256 or s == 1
+        assert bs * hkv * s <= 148 or s == 1          # one wave
+    # tiny grids must be split, saturated grids must not be split at all
+    assert lib.nvllm_paged_decode_plan(1, 4, 1, 40960, 148) == 64
+    assert lib.nvllm_paged_decode_plan(1, 32, 8, 32768, 148) == 16          # power of two: equal chunks per warp
+    assert lib.nvllm_paged_decode_plan(2, 32, 8, 32768, 148) == 8
+    assert lib.nvllm_paged_decode_plan(4, 32, 8, 32768, 148) == 4
+    assert lib.nvllm_paged_decode_plan(5, 4, 1, 32768, 148) == 29           # 16 would idle half the SMs
+    assert lib.nvllm_paged_decode_plan(512, 16, 8, 4096, 148) == 1
+    assert lib.nvllm_paged_decode_plan(128, 2, 1, 4096, 148) == 1            # the tp=8 shard of the 8B shape
+    # opt-in: 0 = the balanced persistent grid, wherever its arrival counters cover the batch
+    monkeypatch.setenv("NVLLM_DECODE_PLAN", "balanced")
+    for bs, hkv, ctx in [(1, 8, 512), (64, 8, 4096), (128, 1, 4096), (1, 1, 40960), (1024, 8, 4096)]:
+        assert lib.nvllm_paged_decode_plan(bs, 4 * hkv, hkv, ctx, 148) == 0
+    assert lib.nvllm_paged_decode_plan(4096, 16, 8, 4096, 148) >= 1          # beyond the arrival-counter area
+    # batch-independent workspace: arrival counters + one head and one tail partial for each of at most 512 CTAs
+    ws0 = lib.nvllm_paged_decode_workspace_bytes(64, 16, 128, 0)
+    assert ws0 == 65536 + 512 * 2 * 8 * 129 * 4
+    assert lib.nvllm_paged_decode_workspace_bytes(1, 4, 128, -10) == ws0
 
 
 def _glue_fixture():

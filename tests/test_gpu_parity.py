@@ -106,6 +106,45 @@ def test_store_matches_reference_triton_kernel(ops):
 
 
 # ------------------------------------------------------------------ paged decode
+# splits >= 1: fixed split-KV grid; (0 | -P, min_chunks): the balanced persistent grid with one CTA per SM | P CTAs,
+# each owning at least `min_chunks` 16-token chunks.  min_chunks = 1 spreads even these small cases over many CTAs, so
+# items are cut into many partials (cross-CTA combine); -1 / -3 / -7 CTAs make one CTA walk many segments.
+BALANCED = [(0, 0), (0, 1), (-1, 1), (-7, 2), (-512, 1)]
+
+
+@pytest.fixture()
+def min_chunks(lib):
+    def _set(n, warps=0):
+        assert lib.nvllm_paged_decode_set_tuning(n, warps) == 0
+    yield _set
+    lib.nvllm_paged_decode_set_tuning(0, 0)
+
+
+@pytest.mark.parametrize("name", list(cases.DECODE_CASES))
+@pytest.mark.parametrize("ctas,mc", BALANCED)
+@pytest.mark.parametrize("warps", [4, 8])       # two 4-warp CTAs per SM (G <= 4) / one 8-warp CTA per SM
+def test_decode_balanced_vs_oracle_and_fixture(ops, min_chunks, name, ctas, mc, warps):
+    c = cases.make_decode_case(name)
+    want = orc.paged_decode_ref(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], c["scale"])
+    g = _cuda(c)
+    min_chunks(mc, warps)
+    for _ in range(2):   # twice: the arrival counters of the shared workspace must have reset themselves
+        got = ops.flash_attn_with_kvcache(g["q"].unsqueeze(1), g["k_cache"], g["v_cache"], g["context_lens"],
+                                          g["block_tables"], softmax_scale=c["scale"], num_splits=ctas)
+        assert _maxerr(got.squeeze(1), want) <= TOL
+    gold = cases.from_bits(np.load(os.path.join(GOLD, f"decode_{name}.npz"))["out"])
+    assert _maxerr(got.squeeze(1), gold) <= TOL   # the reference's own sdpa.math output
+
+
+def test_decode_default_plan_is_the_fixed_grid(ops, monkeypatch):
+    monkeypatch.delenv("NVLLM_DECODE_PLAN", raising=False)
+    assert ops.plan_num_splits(64, 16, 8, 4096) == 1
+    assert ops.plan_num_splits(1, 32, 8, 32768) == 16 and ops.plan_num_splits(2, 32, 8, 32768) == 8
+    assert ops.plan_num_splits(1, 4, 1, 40960) == 64
+    monkeypatch.setenv("NVLLM_DECODE_PLAN", "balanced")   # opt-in: the persistent balanced grid
+    assert ops.plan_num_splits(64, 16, 8, 4096) == 0
+
+
 @pytest.mark.parametrize("name", list(cases.DECODE_CASES))
 @pytest.mark.parametrize("splits", [1, 2, 3, 8])
 def test_decode_vs_oracle_and_fixture(ops, name, splits):
@@ -135,21 +174,29 @@ def test_decode_all_variants(ops, lib):
         lib.nvllm_paged_decode_set_variant(-1)
 
 
-def test_decode_edges(ops):
+def test_decode_edges(ops, min_chunks):
     c = cases.make_decode_case("ragged_g2_tail")
     g = _cuda(c)
+    min_chunks(2)
     # ctx == 0 rows (zero-padded graph rows) -> zeros, other rows unchanged; padding entries may be 0 or -1
     lens = g["context_lens"].clone()
     lens[1] = 0
     tables = g["block_tables"].clone()
     tables[tables < 0] = 0
-    for splits in (1, 4):
+    for splits in (1, 4, 0, -5):
         got = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], lens, tables,
                                           softmax_scale=c["scale"], num_splits=splits)
         ref = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], g["context_lens"], g["block_tables"],
                                           softmax_scale=c["scale"], num_splits=splits)
         assert torch.count_nonzero(got[1]) == 0
-        assert torch.equal(got[0], ref[0]) and torch.equal(got[2:], ref[2:])
+        if splits >= 1:    # the fixed grid gives every (sequence, kv head) its own CTAs: other rows keep their bits
+            assert torch.equal(got[0], ref[0]) and torch.equal(got[2:], ref[2:])
+        else:              # the balanced grid cuts the live work elsewhere once a row is empty
+            assert _maxerr(got[0], ref[0]) <= 4e-3 and _maxerr(got[2:], ref[2:]) <= 4e-3
+    # every row empty (a fully padded captured batch): zeros from the balanced grid too
+    got = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], torch.zeros_like(lens), tables,
+                                      softmax_scale=c["scale"], num_splits=0)
+    assert torch.count_nonzero(got) == 0
     # bs == 0
     empty = ops.flash_attn_with_kvcache(g["q"][:0], g["k_cache"], g["v_cache"], lens[:0], tables[:0],
                                         softmax_scale=c["scale"])
@@ -190,9 +237,12 @@ def test_decode_full_size_properties(ops):
     scale = 128 ** -0.5
     o1 = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=1)
     # (i) split invariance (planned splits and an odd count)
-    for s in (0, 2, 5):
+    for s in (None, 0, -37, 2, 5):
         os_ = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=s)
         assert _maxerr(os_, o1) <= 4e-3
+    # the balanced grid is deterministic and page-placement invariant as well
+    ob = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=0)
+    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=0))
     # (ii) page-permutation invariance: move every page elsewhere, remap the table -> identical bits
     nblk = kc.shape[0]
     perm = torch.randperm(nblk, device=DEV)
@@ -204,6 +254,7 @@ def test_decode_full_size_properties(ops):
     t2[live] = inv[tables[live].long()].to(torch.int32)
     o2 = ops.flash_attn_with_kvcache(q, kc2, vc2, lens, t2, softmax_scale=scale, num_splits=1)
     assert torch.equal(o1, o2)
+    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc2, vc2, lens, t2, softmax_scale=scale, num_splits=0))
     # (iii) linearity in V (K fixed -> identical softmax weights): out(V) + out(V') == out(V + V') up to bf16 rounding
     vb = torch.randn_like(vc)
     oa = ops.flash_attn_with_kvcache(q, kc, vb, lens, tables, softmax_scale=scale, num_splits=1)
@@ -216,6 +267,27 @@ def test_decode_full_size_properties(ops):
         assert _maxerr(o1[b:b + 1], want) <= TOL
 
 
+def test_decode_balanced_ragged_batch(ops):
+    """Ragged live contexts incl. empty rows, 1-token rows and page-boundary lengths, on a wide zero-padded table (the
+    captured-graph layout): the balanced grid (whose ranges cut items anywhere) against the one-CTA-per-item kernel
+    and, for sampled rows, the CPU oracle.  8B-shape heads at tp=2 (16 q / 4 kv)."""
+    ctx = [0, 1, 15, 16, 17, 255, 256, 257, 4096, 513, 0, 3000, 31, 1024, 2047, 2049] * 3 + [8191, 7, 0, 777]
+    bs = len(ctx)
+    q, kc, vc, lens, tables = _full_decode_inputs(bs, [max(x, 1) for x in ctx], 16, 4, seed=11)
+    lens = torch.tensor(ctx, dtype=torch.int32, device=DEV)
+    wide = torch.zeros(bs, 40, dtype=torch.int32, device=DEV)
+    wide[:, :tables.shape[1]] = tables.clamp(min=0)
+    scale = 128 ** -0.5
+    ref = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, num_splits=1)
+    for ctas in (0, -148, -61, -9):
+        got = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, num_splits=ctas)
+        assert _maxerr(got, ref) <= 4e-3, ctas
+        assert torch.count_nonzero(got[lens == 0]) == 0
+    for b in (1, 8, 19, 48):
+        want = orc.paged_decode_ref(q[b:b + 1].cpu(), kc.cpu(), vc.cpu(), lens[b:b + 1].cpu(), wide[b:b + 1].cpu(), scale)
+        assert _maxerr(got[b:b + 1], want) <= TOL
+
+
 def test_decode_long_context_split(ops):
     """configs[4]: Qwen3-8B-shape (32 q / 8 kv), bs=2, ctx 32768, table width 160 (max_model_len 40960)."""
     q, kc, vc, lens, tables = _full_decode_inputs(2, [32768, 30001], 32, 8, seed=3)
@@ -225,6 +297,8 @@ def test_decode_long_context_split(ops):
     o_plan = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale)      # planned split count
     o_one = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=1)
     assert _maxerr(o_plan, o_one) <= 4e-3
+    o_fixed = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, num_splits=9)
+    assert _maxerr(o_fixed, o_one) <= 4e-3
     want = orc.paged_decode_ref(q[1:2].cpu(), kc.cpu(), vc.cpu(), lens[1:2].cpu(), tables[1:2].cpu(), scale)
     assert _maxerr(o_plan[1:2], want) <= TOL
 

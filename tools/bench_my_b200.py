@@ -26,7 +26,7 @@ def setup_paths(args):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import make_integration
-    dst = os.path.join(ROOT, "build", "nanovllm_cuda")
+    dst = make_integration.DEFAULT_DST + f"_{os.getpid()}"
     make_integration.make(os.path.join(ROOT, "baseline", "_ref"), dst)
     sys.path.insert(0, dst)
     # spawned tensor-parallel workers import the engine and the backend by name
@@ -106,12 +106,13 @@ def main():
     ap.add_argument("--shared-prefix", type=int, default=0, help="tokens shared by all prompts (prefix-cache hits)")
     ap.add_argument("--temperature", type=float, default=0.0)
     ap.add_argument("--no-shape-warmup", action="store_true", help="measure exactly like bench_my.py (first point includes compiles)")
+    ap.add_argument("--port", type=int, default=2333, help="NCCL rendezvous port of the first engine (+1 per backend)")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     setup_paths(args)
     results = {}
     for i, backend in enumerate(args.attn_backend):
-        results[backend] = bench_backend(args, backend, 2333 + i)
+        results[backend] = bench_backend(args, backend, args.port + i)
     print("\nbench_my (tok/s, output_len=input_len), tp=%d" % args.tensor_parallel_size)
     for bs in args.batch_sizes:
         print(f"bs={bs:<4d}" + "".join(f"{b:>12s}" for b in args.attn_backend))

@@ -1,8 +1,8 @@
 """Materialise the reference-side binding of INTEGRATION.md on a COPY of the installed reference.
 
-    python tools/make_integration.py [--src baseline/_ref] [--dst build/nanovllm_cuda]
+    python tools/make_integration.py [--src baseline/_ref] [--dst /tmp/nvllm_integration/nanovllm_cuda]
 
-Copies `<src>/nanovllm` to `<dst>/nanovllm` (git-ignored, never committed) and applies exactly the
+Copies `<src>/nanovllm` to `<dst>/nanovllm` (under the system temp directory by default, never inside the repository) and applies exactly the
 edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5/A6/A7), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
@@ -16,6 +16,8 @@ import os
 import shutil
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the generated copy lives OUTSIDE the repository (it is the reference plus a dozen edited lines)
+DEFAULT_DST = os.path.join(__import__("tempfile").gettempdir(), "nvllm_integration", "nanovllm_cuda")
 
 EDITS = [
     # ---- A1: admit the backend name (nanovllm/config.py:6)
@@ -112,6 +114,6 @@ def make(src: str, dst: str) -> str:
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--src", default=os.path.join(ROOT, "baseline", "_ref"))
-    ap.add_argument("--dst", default=os.path.join(ROOT, "build", "nanovllm_cuda"))
+    ap.add_argument("--dst", default=DEFAULT_DST)
     a = ap.parse_args()
     print(make(a.src, a.dst))

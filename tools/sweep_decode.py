@@ -50,11 +50,43 @@ def timeit(fn, flush, iters=12):
     return statistics.median(ts), min(ts)
 
 
+def timeit_graph(fn, ncopy, reps=4, iters=6):
+    """Per-launch device time inside a CUDA graph of ncopy*reps back-to-back launches rotating over the input copies
+    (how the engine runs the kernel: L layers per replay, each on its own cache).  No host launch latency, no event
+    quantisation per launch; adjacent launches may overlap tail and ramp exactly as they do in the engine."""
+    n = ncopy * reps
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for i in range(ncopy):
+            fn(i)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(n):
+            fn(i)
+    g.replay()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a = torch.cuda.Event(enable_timing=True)
+        b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) * 1e3 / n)
+    return statistics.median(ts), min(ts)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shapes", default="c2")
     ap.add_argument("--variants", default="all")
     ap.add_argument("--flash", action="store_true", help="also time flash-attn's kernel on the same inputs")
+    ap.add_argument("--balanced", default="", help="comma list of ctas:min_chunks[:warps] for the balanced grid, e.g. 0:64,0:16:8,-296:64:4")
+    ap.add_argument("--splits", default="", help="override the per-shape split list of the fixed grid (comma list; 'none' skips it)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     lib = _lib.load()
@@ -65,7 +97,12 @@ def main():
         "c2": [(bs, ctx, 16, 8, 16, [0, 1, 2, 4, 8, 16]) for bs in (16, 32, 64) for ctx in (1024, 2048, 4096)],
         "c4": [(128, 4096, 32 // tp, 8 // tp, 16, [0, 1, 2, 4, 8]) for tp in (1, 2, 4, 8)],
         "c5": [(bs, 32768, 32 // tp, 8 // tp, 160, [0, 8, 16, 32, 64]) for bs in (1, 4) for tp in (1, 8)],
+        "c5all": [(bs, 32768, 32 // tp, 8 // tp, 160, [0, 16]) for bs in (1, 2, 4) for tp in (1, 8)],
+        "head": [(64, 4096, 16, 8, 16, [0, 1])],
+        "c4tp1": [(128, 4096, 32, 8, 16, [0])],
+        "c4tp8": [(128, 4096, 4, 1, 16, [0])],
     }
+    os.environ["NVLLM_DECODE_PLAN"] = "splits"   # "planned" below = the fixed-grid plan; the balanced grid is explicit
     sel = []
     for s in args.shapes.split(","):
         sel += shapes[s]
@@ -79,7 +116,7 @@ def main():
             print(json.dumps({"flash": f"unavailable: {e}"}))
     for bs, ctx, hq, hkv, width, split_list in sel:
         one = bs * ctx * hkv * D * 4
-        ncopy = max(1, min(8, -(-(600 << 20) // one)))
+        ncopy = max(1, min(16, -(-(1024 << 20) // one)))
         sets = [make(bs, ctx, hq, hkv, dev, width, seed=c) for c in range(ncopy)]
         q, kc, vc, lens, tab, nbytes = sets[0]
         out = torch.empty_like(q)
@@ -87,13 +124,32 @@ def main():
             f = lambda i: fa(sets[i % ncopy][0].unsqueeze(1), sets[i % ncopy][1], sets[i % ncopy][2], cache_seqlens=lens,
                              block_table=sets[i % ncopy][4], softmax_scale=D ** -0.5, causal=True)
             med, mn = timeit(f, flush)
+            gmed, gmn = timeit_graph(f, ncopy)
             print(json.dumps(dict(impl="flash", bs=bs, ctx=ctx, hq=hq, hkv=hkv, us=round(med, 2), us_min=round(mn, 2),
-                                  gbs=round(nbytes / med / 1e3, 1))), flush=True)
+                                  gbs=round(nbytes / med / 1e3, 1), graph_us=round(gmed, 2),
+                                  graph_gbs=round(nbytes / gmed / 1e3, 1))), flush=True)
+        for spec in [x for x in args.balanced.split(",") if x]:
+            ctas, mc, warps = (int(t) for t in (spec.split(":") + ["0"])[:3])
+            lib.nvllm_paged_decode_set_tuning(mc, warps)
+            ws = torch.zeros(max(ops.decode_workspace_bytes(bs, hq, D, min(ctas, 0)), 16), dtype=torch.uint8, device=dev)
+            f = lambda i: ops.flash_attn_with_kvcache(sets[i % ncopy][0], sets[i % ncopy][1], sets[i % ncopy][2], lens,
+                                                      sets[i % ncopy][4], softmax_scale=D ** -0.5, num_splits=min(ctas, 0),
+                                                      out=out, workspace=ws)
+            med, mn = timeit(f, flush)
+            gmed, gmn = timeit_graph(f, ncopy)
+            print(json.dumps(dict(impl="cuda-balanced", ctas=ctas, min_chunks=mc, warps=warps, bs=bs, ctx=ctx, hq=hq, hkv=hkv,
+                                  us=round(med, 2), us_min=round(mn, 2), gbs=round(nbytes / med / 1e3, 1),
+                                  graph_us=round(gmed, 2), graph_gbs=round(nbytes / gmed / 1e3, 1))), flush=True)
+        lib.nvllm_paged_decode_set_tuning(0, 0)
+        if args.splits == "none":
+            split_list = []
+        elif args.splits:
+            split_list = [int(x) for x in args.splits.split(",")]
         for v in variants:
             lib.nvllm_paged_decode_set_variant(v)
             done = set()
             for s in split_list:
-                ns = s if s > 0 else ops.plan_num_splits(bs, hkv, tab.size(1) * BLOCK)
+                ns = s if s > 0 else ops.plan_num_splits(bs, hq, hkv, tab.size(1) * BLOCK)
                 if ctx // ns < 32 or (s > 0 and ns in done):
                     continue
                 done.add(ns)
@@ -102,9 +158,11 @@ def main():
                                                           sets[i % ncopy][4], softmax_scale=D ** -0.5, num_splits=ns,
                                                           out=out, workspace=ws)
                 med, mn = timeit(f, flush)
+                gmed, gmn = timeit_graph(f, ncopy)
                 print(json.dumps(dict(impl="cuda", variant=v, bs=bs, ctx=ctx, hq=hq, hkv=hkv, splits=ns,
                                       planned=(s == 0), us=round(med, 2), us_min=round(mn, 2),
-                                      gbs=round(nbytes / med / 1e3, 1))), flush=True)
+                                      gbs=round(nbytes / med / 1e3, 1), graph_us=round(gmed, 2),
+                                      graph_gbs=round(nbytes / gmed / 1e3, 1))), flush=True)
         del q, kc, vc, sets
         torch.cuda.empty_cache()
     lib.nvllm_paged_decode_set_variant(-1)
