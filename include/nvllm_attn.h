@@ -169,6 +169,12 @@ NVLLM_API int32_t nvllm_paged_decode_num_variants(void);
  * least (fewer CTAs take part when the live work is small; <= 0 = default), and
  * warps per CTA (4 = two CTAs per SM, needs G <= 4; 8 = one CTA per SM; else automatic). */
 NVLLM_API int nvllm_paged_decode_set_tuning(int32_t min_chunks_per_cta, int32_t warps_per_cta);
+/* Tuning hook of the split-KV grid: when the whole grid is one wave, the split CTAs
+ * of a (sequence, kv head) form thread-block clusters and merge through the leader's
+ * shared memory (one workspace partial per cluster, none when the cluster holds all
+ * splits).  0 = automatic (largest of 8/4/2 that divides num_splits and is
+ * co-resident), 1 = never, 2/4/8/16 = that size or none. */
+NVLLM_API int nvllm_paged_decode_set_cluster(int32_t cluster);
 
 /* ------------------------------------------------------------------------
  * (3) varlen causal prefill with optional paged prefix (prefix cache).

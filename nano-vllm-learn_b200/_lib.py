@@ -28,6 +28,7 @@ SIGNATURES = {
     "nvllm_paged_decode_set_variant": (c_int, [c_int32]),
     "nvllm_paged_decode_num_variants": (c_int32, []),
     "nvllm_paged_decode_set_tuning": (c_int, [c_int32, c_int32]),
+    "nvllm_paged_decode_set_cluster": (c_int, [c_int32]),
     "nvllm_varlen_prefill": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int64,
                                      c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p,
                                      c_int64, c_int32, c_int32, c_int32, c_int32, c_float, c_void_p]),

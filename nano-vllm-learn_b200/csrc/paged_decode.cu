@@ -44,8 +44,30 @@ struct DecodeParams {
   int32_t block_size;
   int32_t block_shift; // log2(block_size) when it is a power of two, else -1
   int32_t num_splits;
+  int32_t cluster;     // split CTAs per thread-block cluster (1 = no cluster); divides num_splits
   float scale_log2;    // softmax scale * log2(e)
 };
+
+// Bytes of the cluster leader's exchange area: one normalised fp32 row (128 values + log2-sum-exp) per member and query row.
+constexpr int kXchgRow = kHeadDim + 1;
+static inline int cluster_xchg_bytes(int cluster, int group) { return cluster * group * kXchgRow * 4; }
+
+__device__ __forceinline__ uint32_t cluster_map_shared(uint32_t local_addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;\n" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_arrive_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
 
 template <int CHUNK, int WARPS, int STAGES>
 struct DecodeCfg {
@@ -96,6 +118,9 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int G = p.group;
+  // every member of the cluster has started (its shared memory exists) before anyone pushes into the leader's: phase 0
+  // of the cluster barrier is arrived at here and waited for just before the push
+  if (p.cluster > 1) cluster_arrive_relaxed();
 
   const int ctx = __ldg(p.context_lens + b);
   const int n_chunks = (ctx + CHUNK - 1) / CHUNK;
@@ -297,6 +322,16 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   }
   __syncthreads();
 
+  // With clusters the split CTAs of one (sequence, kv head) merge through the leader's shared memory first: every member
+  // pushes its normalised rows (DSMEM stores), one cluster barrier, and the leader alone goes on -- with one partial per
+  // CLUSTER for the device-wide merge below, or straight to the output when the cluster holds all the splits.
+  const int C = p.cluster;
+  const int S = p.num_splits / C;       // partials per (sequence, kv head) in the workspace
+  const int slot_of_cta = split / C;
+  float* const xchg = reinterpret_cast<float*>(smem + Cfg::kSmemBytes);   // leader: [C][G][129], outside the pipeline rings
+  const uint32_t xchg_leader = C > 1 ? cluster_map_shared(smem_u32(xchg), 0) : 0u;
+  const int crank = split % C;
+  if (C > 1) cluster_wait();
   for (int idx = threadIdx.x; idx < G * kHeadDim; idx += WARPS * 32) {
     const int row = idx >> 7;
     const int d = idx & (kHeadDim - 1);
@@ -313,16 +348,55 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
       }
     }
     const float val = den > 0.f ? num / den : 0.f;
+    const float lse = den > 0.f ? M * p.scale_log2 + fast_log2(den) : -INFINITY;
     const int h = kvh * G + row;
     if (p.num_splits == 1) {
       p.out[(static_cast<int64_t>(b) * p.num_q_heads + h) * kHeadDim + d] = __float2bfloat16_rn(val);
+    } else if (C > 1) {
+      const uint32_t dst = xchg_leader + ((crank * G + row) * kXchgRow + d) * 4;
+      st_cluster_f32(dst, val);
+      if (d == 0) st_cluster_f32(dst + kHeadDim * 4, lse);
     } else {
-      const int64_t slot = (static_cast<int64_t>(b) * p.num_q_heads + h) * p.num_splits + split;
+      const int64_t slot = (static_cast<int64_t>(b) * p.num_q_heads + h) * S + slot_of_cta;
       p.part_o[slot * kHeadDim + d] = val;
-      if (d == 0) p.part_lse[slot] = den > 0.f ? M * p.scale_log2 + fast_log2(den) : -INFINITY;
+      if (d == 0) p.part_lse[slot] = lse;
     }
   }
   if (p.num_splits == 1) return;
+  if (C > 1) {
+    cluster_sync_all();          // release/acquire at cluster scope: the pushed rows are visible to the leader
+    if (crank != 0) return;
+    for (int idx = threadIdx.x; idx < G * kHeadDim; idx += WARPS * 32) {
+      const int row = idx >> 7;
+      const int d = idx & (kHeadDim - 1);
+      float L = -INFINITY;
+      for (int c = 0; c < C; ++c) L = fmaxf(L, xchg[(c * G + row) * kXchgRow + kHeadDim]);
+      float num = 0.f, den = 0.f;
+      if (L > -INFINITY) {
+#pragma unroll 4
+        for (int c = 0; c < C; ++c) {
+          const float* src = xchg + (c * G + row) * kXchgRow;
+          const float wgt = fast_exp2(src[kHeadDim] - L);
+          num += wgt * src[d];
+          den += wgt;
+        }
+      }
+      const float val = den > 0.f ? num / den : 0.f;
+      const int h = kvh * G + row;
+      if (S == 1) {
+        p.out[(static_cast<int64_t>(b) * p.num_q_heads + h) * kHeadDim + d] = __float2bfloat16_rn(val);
+      } else {
+        const int64_t slot = (static_cast<int64_t>(b) * p.num_q_heads + h) * S + slot_of_cta;
+        p.part_o[slot * kHeadDim + d] = val;
+        if (d == 0) p.part_lse[slot] = den > 0.f ? L + fast_log2(den) : -INFINITY;
+      }
+    }
+    if (S == 1) {
+      NVLLM_TRACE(4);
+      NVLLM_TRACE(5);
+      return;
+    }
+  }
 
   // ---- fused combine: the LAST split CTA of this (sequence, kv head) to arrive merges all partials.
   // out = sum_s 2^(lse_s - L) O_s / sum_s 2^(lse_s - L).  Saves the separate combine launch (5-6 us).
@@ -332,7 +406,7 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
     int32_t* cnt = p.counters + b * gridDim.y + kvh;
     int old;
     asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;\n" : "=r"(old) : "l"(cnt) : "memory");
-    s_is_last = (old == p.num_splits - 1);
+    s_is_last = (old == S - 1);
     if (s_is_last) *cnt = 0;   // self-resetting: the next launch (or graph replay) starts from zero
   }
   __syncthreads();   // ... and thread 0's acquire happens-before every thread's partial loads
@@ -344,7 +418,6 @@ __global__ void __launch_bounds__(Cfg::kWarps * 32) paged_decode_kernel(const De
   {
     constexpr int NTHR = WARPS * 32;
     constexpr int kBatch = 16;
-    const int S = p.num_splits;
     float* const s_lse = reinterpret_cast<float*>(smem);                    // [G][S], S <= 128
     float4* const s_acc = reinterpret_cast<float4*>(smem + 8 * 128 * 4);    // [groups][G * 32]
     float* const s_den = reinterpret_cast<float*>(smem + 8 * 128 * 4 + NTHR * 16);
@@ -450,16 +523,84 @@ static int g_variant = -1;
 
 static int sm_count_cached() { return device_sm_count(); }
 
+// Largest cluster (<= 16 split CTAs of one (sequence, kv head), a divisor of num_splits) whose exchange area fits beside
+// the pipeline rings and for which the WHOLE grid is co-resident (cudaOccupancyMaxActiveClusters): a cluster waiting for
+// a second wave would idle the SMs its members hold.  1 = no clusters.  `force`: 0 automatic, > 0 that size or none.
+static int g_force_cluster = 0;
+constexpr int kMaxDecodeSmem = 226 * 1024;   // 227 KB opt-in limit minus the kernel's few static bytes
 template <class Cfg>
-static cudaError_t launch_decode(const DecodeParams& p, int bs, int hkv, cudaStream_t stream) {
+static int pick_cluster(const DecodeParams& p, int bs, int hkv) {
+  if (p.num_splits <= 1 || g_force_cluster == 1) return 1;
+  const int64_t ctas = static_cast<int64_t>(p.num_splits) * hkv * bs;
+  if (ctas > sm_count_cached()) return 1;
+  struct Seen { int dev, c, g, n; };
+  static Seen seen[64];
+  static int n_seen = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+  // automatic: portable sizes only -- 16 (opt-in size) measured no faster than 8 on B200 and constrains placement
+  for (int c = g_force_cluster == 16 ? 16 : 8; c >= 2; c >>= 1) {
+    if (g_force_cluster > 1 && c != g_force_cluster) continue;
+    if (p.num_splits % c) continue;
+    const int smem = Cfg::kSmemBytes + cluster_xchg_bytes(c, p.group);
+    if (smem > kMaxDecodeSmem) continue;
+    int max_clusters = -1;
+    for (int i = 0; i < n_seen; ++i)
+      if (seen[i].dev == dev && seen[i].c == c && seen[i].g == p.group) max_clusters = seen[i].n;
+    if (max_clusters < 0) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(c * 64, 1, 1);
+      cfg.blockDim = dim3(Cfg::kWarps * 32, 1, 1);
+      cfg.dynamicSmemBytes = smem;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = c;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, paged_decode_kernel<Cfg>, &cfg) != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+      }
+      max_clusters = n;
+      if (n_seen < 64) seen[n_seen++] = Seen{dev, c, p.group, n};
+    }
+    if (static_cast<int64_t>(max_clusters) * c >= ctas) return c;
+  }
+  return 1;
+}
+
+template <class Cfg>
+static cudaError_t launch_decode(DecodeParams p, int bs, int hkv, cudaStream_t stream) {
   static PerDeviceOnce configured;
   cudaError_t e0 = once_per_device(configured, [] {
-    return cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kMaxDecodeSmem);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(paged_decode_kernel<Cfg>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   });
   if (e0 != cudaSuccess) return e0;
   dim3 grid(p.num_splits, hkv, bs);
-  paged_decode_kernel<Cfg><<<grid, Cfg::kWarps * 32, Cfg::kSmemBytes, stream>>>(p);
-  return cudaGetLastError();
+  p.cluster = pick_cluster<Cfg>(p, bs, hkv);
+  if (p.cluster == 1) {
+    paged_decode_kernel<Cfg><<<grid, Cfg::kWarps * 32, Cfg::kSmemBytes, stream>>>(p);
+    return cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(Cfg::kWarps * 32, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes + cluster_xchg_bytes(p.cluster, p.group);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = p.cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, paged_decode_kernel<Cfg>, p);
 }
 
 }  // namespace nvllm
@@ -529,6 +670,11 @@ int nvllm_paged_decode_set_tuning(int32_t min_chunks_per_cta, int32_t warps_per_
   return NVLLM_OK;
 }
 int32_t nvllm_paged_decode_num_variants(void) { return nvllm::kNumVariants; }
+int nvllm_paged_decode_set_cluster(int32_t cluster) {
+  if (cluster != 0 && cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8 && cluster != 16) return NVLLM_ERR_BAD_ARG;
+  nvllm::g_force_cluster = cluster;
+  return NVLLM_OK;
+}
 
 int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
                        int64_t cache_block_stride, int64_t cache_token_stride, const int32_t* block_tables,
@@ -614,6 +760,7 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
   for (int sh = 0; sh < 31; ++sh)
     if ((1 << sh) == block_size) p.block_shift = sh;
   p.num_splits = num_splits;
+  p.cluster = 1;
   p.scale_log2 = scale * kLog2e;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);

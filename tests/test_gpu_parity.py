@@ -138,11 +138,14 @@ def test_decode_balanced_vs_oracle_and_fixture(ops, min_chunks, name, ctas, mc, 
 
 def test_decode_default_plan_is_the_fixed_grid(ops, monkeypatch):
     monkeypatch.delenv("NVLLM_DECODE_PLAN", raising=False)
+    monkeypatch.setattr(ops, "_PLAN_CACHE", {})
     assert ops.plan_num_splits(64, 16, 8, 4096) == 1
     assert ops.plan_num_splits(1, 32, 8, 32768) == 16 and ops.plan_num_splits(2, 32, 8, 32768) == 8
     assert ops.plan_num_splits(1, 4, 1, 40960) == 64
     monkeypatch.setenv("NVLLM_DECODE_PLAN", "balanced")   # opt-in: the persistent balanced grid
+    monkeypatch.setattr(ops, "_PLAN_CACHE", {})
     assert ops.plan_num_splits(64, 16, 8, 4096) == 0
+    monkeypatch.setattr(ops, "_PLAN_CACHE", {})
 
 
 @pytest.mark.parametrize("name", list(cases.DECODE_CASES))
@@ -157,6 +160,31 @@ def test_decode_vs_oracle_and_fixture(ops, name, splits):
     assert _maxerr(got.squeeze(1), want) <= TOL
     gold = cases.from_bits(np.load(os.path.join(GOLD, f"decode_{name}.npz"))["out"])
     assert _maxerr(got.squeeze(1), gold) <= TOL   # the reference's own sdpa.math output
+
+
+@pytest.mark.parametrize("name", list(cases.DECODE_CASES))
+@pytest.mark.parametrize("splits,cluster", [(2, 2), (4, 4), (8, 8), (16, 16), (8, 2), (16, 4), (12, 4), (16, 0), (6, 0)])
+def test_decode_cluster_merge_vs_oracle_and_fixture(ops, lib, name, splits, cluster):
+    """One-wave grids: the split CTAs of a (sequence, kv head) merge through the cluster leader's shared memory; one
+    workspace partial per cluster (splits / cluster of them), none when the cluster holds every split."""
+    c = cases.make_decode_case(name)
+    want = orc.paged_decode_ref(c["q"], c["k_cache"], c["v_cache"], c["context_lens"], c["block_tables"], c["scale"])
+    g = _cuda(c)
+    assert lib.nvllm_paged_decode_set_cluster(3) != 0
+    assert lib.nvllm_paged_decode_set_cluster(cluster) == 0
+    try:
+        for _ in range(2):   # twice: the arrival counters must have reset themselves
+            got = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], g["context_lens"], g["block_tables"],
+                                              softmax_scale=c["scale"], num_splits=splits)
+            assert _maxerr(got, want) <= TOL
+        lib.nvllm_paged_decode_set_cluster(1)
+        flat = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], g["context_lens"], g["block_tables"],
+                                           softmax_scale=c["scale"], num_splits=splits)
+        assert _maxerr(got, flat) <= 4e-3      # same partition of the tokens, a different merge tree
+    finally:
+        lib.nvllm_paged_decode_set_cluster(0)
+    gold = cases.from_bits(np.load(os.path.join(GOLD, f"decode_{name}.npz"))["out"])
+    assert _maxerr(got, gold) <= TOL
 
 
 def test_decode_all_variants(ops, lib):

@@ -32,6 +32,13 @@ def make(bs, ctx, hq, hkv, dev, width=None, seed=0):
     return q, kc, vc, lens, tab, nbytes
 
 
+def share_table(sets):
+    """One block table and context_lens for every cache copy: the layers of a model share the step's table while each
+    owns its cache, so the metadata is L2-resident when the K/V bytes are not."""
+    t, lens = sets[0][4], sets[0][3]
+    return [(q, kc, vc, lens, t, nb) for q, kc, vc, _, _, nb in sets]
+
+
 def timeit(fn, flush, iters=12):
     """fn(i) runs on the i-th copy of the inputs; copies rotate so the working set exceeds L2 and no
     dirty-line flush pollutes the timed launch."""
@@ -86,6 +93,7 @@ def main():
     ap.add_argument("--variants", default="all")
     ap.add_argument("--flash", action="store_true", help="also time flash-attn's kernel on the same inputs")
     ap.add_argument("--balanced", default="", help="comma list of ctas:min_chunks[:warps] for the balanced grid, e.g. 0:64,0:16:8,-296:64:4")
+    ap.add_argument("--clusters", default="0", help="comma list of cluster sizes of the split-KV grid (0 auto, 1 off, 2/4/8/16)")
     ap.add_argument("--splits", default="", help="override the per-shape split list of the fixed grid (comma list; 'none' skips it)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
@@ -102,7 +110,7 @@ def main():
         "c4tp1": [(128, 4096, 32, 8, 16, [0])],
         "c4tp8": [(128, 4096, 4, 1, 16, [0])],
     }
-    os.environ["NVLLM_DECODE_PLAN"] = "splits"   # "planned" below = the fixed-grid plan; the balanced grid is explicit
+    os.environ.pop("NVLLM_DECODE_PLAN", None)    # "planned" below = the split-KV plan; the balanced grid is explicit
     sel = []
     for s in args.shapes.split(","):
         sel += shapes[s]
@@ -117,7 +125,7 @@ def main():
     for bs, ctx, hq, hkv, width, split_list in sel:
         one = bs * ctx * hkv * D * 4
         ncopy = max(1, min(16, -(-(1024 << 20) // one)))
-        sets = [make(bs, ctx, hq, hkv, dev, width, seed=c) for c in range(ncopy)]
+        sets = share_table([make(bs, ctx, hq, hkv, dev, width, seed=c) for c in range(ncopy)])
         q, kc, vc, lens, tab, nbytes = sets[0]
         out = torch.empty_like(q)
         if fa is not None:
@@ -157,12 +165,17 @@ def main():
                 f = lambda i: ops.flash_attn_with_kvcache(sets[i % ncopy][0], sets[i % ncopy][1], sets[i % ncopy][2], lens,
                                                           sets[i % ncopy][4], softmax_scale=D ** -0.5, num_splits=ns,
                                                           out=out, workspace=ws)
-                med, mn = timeit(f, flush)
-                gmed, gmn = timeit_graph(f, ncopy)
-                print(json.dumps(dict(impl="cuda", variant=v, bs=bs, ctx=ctx, hq=hq, hkv=hkv, splits=ns,
-                                      planned=(s == 0), us=round(med, 2), us_min=round(mn, 2),
-                                      gbs=round(nbytes / med / 1e3, 1), graph_us=round(gmed, 2),
-                                      graph_gbs=round(nbytes / gmed / 1e3, 1))), flush=True)
+                for cl in [int(x) for x in args.clusters.split(",")]:
+                    if ns == 1 and cl != 0:
+                        continue
+                    assert lib.nvllm_paged_decode_set_cluster(cl) == 0
+                    med, mn = timeit(f, flush)
+                    gmed, gmn = timeit_graph(f, ncopy)
+                    print(json.dumps(dict(impl="cuda", variant=v, bs=bs, ctx=ctx, hq=hq, hkv=hkv, splits=ns, cluster=cl,
+                                          planned=(s == 0), us=round(med, 2), us_min=round(mn, 2),
+                                          gbs=round(nbytes / med / 1e3, 1), graph_us=round(gmed, 2),
+                                          graph_gbs=round(nbytes / gmed / 1e3, 1))), flush=True)
+                lib.nvllm_paged_decode_set_cluster(0)
         del q, kc, vc, sets
         torch.cuda.empty_cache()
     lib.nvllm_paged_decode_set_variant(-1)

@@ -21,7 +21,7 @@ from nano_vllm_learn_b200 import _lib  # noqa: E402
 
 lib = _lib.load_tools()   # python nano-vllm-learn_b200/build.py --tools
 from nano_vllm_learn_b200 import ops  # noqa: E402
-from sweep_decode import make  # noqa: E402
+from sweep_decode import make, share_table  # noqa: E402
 
 D, BLOCK = 128, 256
 
@@ -35,12 +35,14 @@ def main():
     ap.add_argument("--width", type=int, default=160)
     ap.add_argument("--splits", type=int, default=18)
     ap.add_argument("--variant", type=int, default=-1)
+    ap.add_argument("--cluster", type=int, default=0)
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     lib.nvllm_paged_decode_set_variant(a.variant)
+    lib.nvllm_paged_decode_set_cluster(a.cluster)
     one = a.bs * a.ctx * a.hkv * D * 4
     ncopy = max(2, min(16, -(-(1024 << 20) // one)))
-    sets = [make(a.bs, a.ctx, a.hq, a.hkv, dev, a.width, seed=c) for c in range(ncopy)]
+    sets = share_table([make(a.bs, a.ctx, a.hq, a.hkv, dev, a.width, seed=c) for c in range(ncopy)])
     lens = sets[0][3]
     out = torch.empty_like(sets[0][0])
     ws = torch.zeros(max(ops.decode_workspace_bytes(a.bs, a.hq, D, a.splits), 16), dtype=torch.uint8, device=dev)
@@ -76,7 +78,7 @@ def main():
                "exit_last": rel[fin, 5].max().item() if fin.any() else None}
         rows.append({k: (round(v, 2) if v is not None else None) for k, v in row.items()})
     # a launch behind its predecessor: entry times are spread because CTAs of the previous launch still hold SMs
-    print(json.dumps(dict(shape=dict(bs=a.bs, ctx=a.ctx, hq=a.hq, hkv=a.hkv, splits=a.splits, variant=a.variant, ctas=n_cta),
+    print(json.dumps(dict(shape=dict(bs=a.bs, ctx=a.ctx, hq=a.hq, hkv=a.hkv, splits=a.splits, variant=a.variant, cluster=a.cluster, ctas=n_cta),
                           us_since_first_cta_entry=rows)))
 
 
