@@ -22,6 +22,10 @@ extern "C" {
  * behind them (>= 147456 bytes in all). */
 NVLLM_API void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr);
 
+/* tools/sweep_prefill.py: of every 8 column pairs of an unmasked S tile, how many take the FMA-pipe cubic
+ * instead of MUFU ex2 in the tcgen05 prefill kernel (0..5; < 0 restores the product default). */
+NVLLM_API void nvllm_varlen_prefill_set_exp2_poly(int pairs_of_8);
+
 /* tools/trace_decode.py: when non-NULL, thread 0 of every CTA of the fixed-grid paged-decode kernel stamps
  * %globaltimer (ns) at six protocol points into buffer[cta * 8 + k]: 0 entry, 1 first copies issued, 2 first chunk
  * landed, 3 main loop done, 4 partial published, 5 exit (combining CTA only); cta = (b * Hkv + kvh) * S + split. */

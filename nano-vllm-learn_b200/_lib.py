@@ -65,6 +65,7 @@ SIGNATURES = {
 # include/nvllm_tools.h (lib/libnvllm_tools.so only; tools/*.py call load_tools())
 TOOLS_SIGNATURES = {
     "nvllm_varlen_prefill_set_debug_buffer": (None, [c_void_p]),
+    "nvllm_varlen_prefill_set_exp2_poly": (None, [c_int]),
     "nvllm_paged_decode_set_trace": (c_int, [c_void_p]),
     "nvllm_debug_stream_read": (c_int, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
 }

@@ -5,19 +5,20 @@
 //
 // Persistent kernel: one CTA per SM loops over work items (sequence, q head, PAIR of 128-query tiles A and
 // B); barrier phases run on across items, so the TMA producer prefetches the next item's Q/K/V while the
-// softmax warpgroups drain the current item's output.  384 threads:
-//   warpgroup 0 (warps 0-3)   softmax of tile A: one query row per thread (TMEM lane == row)
-//   warpgroup 1 (warps 4-7)   softmax of tile B
-//   warp 8                    TMA producer (one elected lane)
-//   warp 9                    tcgen05.mma issuer (one elected lane) + TMEM allocator
-//   warps 10-11               idle (complete the third warpgroup for setmaxnreg)
+// softmax warpgroups drain the current item's output.  640 threads:
+//   warpgroups 0-3 (warps 0-15) softmax: warpgroup g owns columns 32g..32g+31 of EVERY S tile (A and B) and of
+//                               every O tile, one query row per thread (warps w, w+4, w+8, w+12 share TMEM lanes)
+//   warp 16                     TMA producer (one elected lane)
+//   warp 17                     tcgen05.mma issuer (one elected lane) + TMEM allocator
+//   warps 18-19                 idle (complete the fifth warpgroup for setmaxnreg)
 // Both tiles share every K/V tile (loaded once).  Per 128-key tile j and query tile t in {A, B}:
 //   S_t = Q_t . K_j^T      SS MMA, 8 x (M128 N128 K16); Q_t, K_j K-major SW128 in shared memory
-//   softmax warpgroup t:   S row -> registers, running max with lazy rescale (only when the max grows by
-//                          more than 2^8), P = exp2(S*c - m*c) in bf16 written back over S (P aliases S)
+//   softmax (both groups): half an S row -> registers, running max (halves agree through shared memory) with lazy
+//                          rescale (only when the max grows by more than 2^8), P = exp2(S*c - m*c) in bf16 written
+//                          back over S (P aliases S); part of the exponentials run on the FMA pipe (exp2_poly2)
 //   O_t += P . V_j         TS MMA: A = P from TMEM, B = V_j MN-major SW128 in shared memory; O_t stays in TMEM
-// The issuer alternates A and B, so the tensor pipe runs one tile's MMAs while the other tile's
-// warpgroup does its softmax (ping-pong).  TMEM: S_A S_B O_A O_B = 4 x 128 columns = all 512.
+// The issuer alternates A and B, so the tensor pipe runs one tile's MMAs while all eight softmax warps work on the
+// other tile (ping-pong).  TMEM: S_A S_B O_A O_B = 4 x 128 columns = all 512.
 #include "prefill_params.cuh"
 #include "tcgen05.cuh"
 #ifdef NVLLM_TOOLS_BUILD
@@ -33,12 +34,20 @@ constexpr int TN = 128;                      // keys per tile
 constexpr int kHalfBytes = 128 * 128;        // [128 rows][64 bf16] = 16 KB, one SW128 half of a tile
 constexpr int kTileBytes = 2 * kHalfBytes;   // 32 KB
 constexpr int kStages = 2;                   // K/V ring depth
-constexpr int kThreads = 384;
+constexpr int kSoftmaxGroups = 2;            // softmax warpgroups
+constexpr int kTeams = 1;                    // 2: warpgroups 0-1 work on query tile A, 2-3 on tile B; 1: all on every tile
+constexpr int kSoftmaxWarps = 4 * kSoftmaxGroups;
+constexpr int kThreads = (kSoftmaxWarps + 4) * 32;   // + one warpgroup: TMA producer, MMA issuer, two idle warps
+constexpr int kRegsSoftmax = kSoftmaxGroups == 2 ? 200 : 104;   // 512 * 104 + 128 * 64 < 64 K: asking for exactly the whole file never completes   // setmaxnreg budgets: 128 * (kColGroups * soft + other) <= 64 K
+constexpr int kRegsOther = kSoftmaxGroups == 2 ? 96 : 64;
 constexpr int kSmemQ = 0;                                    // Q_A, Q_B
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kStages * kTileBytes;
 constexpr int kSmemBar = kSmemV + kStages * kTileBytes;      // 192 KB
-constexpr int kSmemBytes = kSmemBar + 256 + 1024;            // barriers + alignment slack
+constexpr int kSmemXchg = kSmemBar + 256;                    // row max / row sum exchange between the column halves
+constexpr int kSmemStage = kSmemXchg + 2 * kSoftmaxGroups * 128 * 4;   // per-warp output staging: 32 rows x 80 B
+constexpr int kStagePitch = 80;
+constexpr int kSmemBytes = kSmemStage + kSoftmaxWarps * 32 * kStagePitch + 1024;   // + alignment slack
 constexpr uint32_t kTmemCols = 512;
 constexpr float kRescaleThreshold = 8.f;     // log2 units: P stays <= 2^8 relative to the stale max
 
@@ -66,9 +75,21 @@ struct Item {
   bool live;
 };
 
-__device__ __forceinline__ Item decode_item(const PrefillParams& p, int w, int num_pairs, int batch) {
+// `slot` = CTA + round * grid.  Rounds alternate direction (CTA i takes item i of an even round and item grid-1-i of an
+// odd one): with heavy-first items a plain round-robin hands CTA 0 the heaviest item of every round (1 x 8192: the
+// busiest CTA carried 29 % more than the mean, 4 % this way).
+__device__ __forceinline__ Item decode_item(const PrefillParams& p, int slot, int num_pairs, int batch) {
   Item it;
   const int per_pair = p.num_q_heads * batch;
+  const int grid = static_cast<int>(gridDim.x);
+  const int round = slot / grid, cta = slot % grid;
+  const int w = round * grid + ((round & 1) ? grid - 1 - cta : cta);
+  if (w >= num_pairs * per_pair) {   // the last round may be partial
+    it.seq = it.h = it.kvh = it.q0 = it.k0 = it.Lq = it.Lk = it.m0 = it.shift = it.n_tiles = 0;
+    it.n_t[0] = it.n_t[1] = 0;
+    it.live = false;
+    return it;
+  }
   const int mbp = num_pairs - 1 - w / per_pair;
   const int rem = w % per_pair;
   it.seq = rem / p.num_q_heads;
@@ -91,13 +112,50 @@ __device__ __forceinline__ Item decode_item(const PrefillParams& p, int w, int n
 }
 
 
+// exp2 of a pair on the FMA pipe (no MUFU): round to the nearest integer n by the 1.5 * 2^23 trick, a cubic for
+// 2^f on f in [-0.5, 0.5] (max relative error 7.5e-5 = 2^-13.7, far below the bf16 rounding of P), n added to the
+// exponent field.  x is clamped to >= -125 (2^-125 stands in for anything smaller, -inf included); x <= ~9 here.
+// The MUFU unit makes 4 ex2 per clock per SM sub-partition: for a 128 x 128 S tile that is as long as the tile's two
+// MMAs take, so part of every row goes through this path (FFMA2 / FADD2 are two-wide) to pull the softmax off the
+// critical path.
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  constexpr float kMagic = 12582912.f;   // 1.5 * 2^23
+  x.x = fmaxf(x.x, -125.f);
+  x.y = fmaxf(x.y, -125.f);
+  const float2 t = __fadd2_rn(x, make_float2(kMagic, kMagic));
+  const float2 r = __fadd2_rn(t, make_float2(-kMagic, -kMagic));
+  const float2 f = __ffma2_rn(r, make_float2(-1.f, -1.f), x);
+  float2 q = __ffma2_rn(make_float2(0.05517147481441498f, 0.05517147481441498f), f,
+                        make_float2(0.242610901594162f, 0.242610901594162f));
+  q = __ffma2_rn(q, f, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  q = __ffma2_rn(q, f, make_float2(0.9999281167984009f, 0.9999281167984009f));
+  float2 out;
+  out.x = __int_as_float(__float_as_int(q.x) + (__float_as_int(t.x) << 23));
+  out.y = __int_as_float(__float_as_int(q.y) + (__float_as_int(t.y) << 23));
+  return out;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;\n" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
 // Debug-build timeline (tools/trace_prefill.py): CTA 0 stamps clock64() at the protocol points of its first
 // work item into debug[32768 + (role * 64 + step) * 8 + k]; role 0 = MMA issuer, 1 = softmax A, 2 = softmax B.
 __device__ __forceinline__ void trace_stamp(float* debug, int role, int step, int k) {
   if (step < 64) reinterpret_cast<uint32_t*>(debug)[32768 + (role * 64 + step) * 8 + k] = static_cast<uint32_t>(clock64());
 }
 
-template <bool kDebug>
+// kEmu: of every 8 column pairs of an unmasked S tile, how many take exp2_poly2 instead of the MUFU unit.
+// Item-level timeline of CTA 0 (tools/trace_prefill.py --items): debug[32768 + (4 * 64 + item) * 8 + k], k: 0 softmax
+// threads start the item, 1 its first S tile is ready, 2 its last P has been handed over, 3 the O tiles are final,
+// 4 the output stores are issued; 5 the MMA issuer starts the item, 6 its first QK is issued (Q and K landed), 7 its
+// last PV is issued.
+__device__ __forceinline__ void item_stamp(float* debug, int item, int k) {
+  if (item < 64) reinterpret_cast<uint32_t*>(debug)[32768 + (4 * 64 + item) * 8 + k] = static_cast<uint32_t>(clock64());
+}
+
+template <bool kDebug, int kEmu>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                        const __grid_constant__ CUtensorMap tm_v, const PrefillParams p, const int num_pairs,
@@ -109,20 +167,22 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
-  const int total_items = num_pairs * p.num_q_heads * batch;
+  // slots of this launch: whole rounds of the grid (decode_item marks the tail of the last round dead)
+  const int total_items = (num_pairs * p.num_q_heads * batch + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x) *
+                          static_cast<int>(gridDim.x);
 
   const uint32_t bar0 = smem + kSmemBar;
   auto bar = [&](int i) -> uint32_t { return bar0 + 8u * static_cast<uint32_t>(i); };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem_gen + kSmemBar + 8 * kNumBars);
 
-  if (warp == 8 && lane == 0) {
+  if (warp == kSoftmaxWarps && lane == 0) {
     for (int t = 0; t < 2; ++t) {
       tc::mbar_init(bar(kQFull + t), 1);
       tc::mbar_init(bar(kSFull + t), 1);
-      tc::mbar_init(bar(kPFull + t), 128);
+      tc::mbar_init(bar(kPFull + t), kSoftmaxWarps * 32 / kTeams);
       tc::mbar_init(bar(kOFull + t), 1);
       tc::mbar_init(bar(kQEmpty + t), 1);
-      tc::mbar_init(bar(kOEmpty + t), 128);
+      tc::mbar_init(bar(kOEmpty + t), kSoftmaxWarps * 32 / kTeams);
     }
     for (int s = 0; s < kStages; ++s) {
       tc::mbar_init(bar(kKFull + s), 1);
@@ -131,7 +191,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     }
     tc::fence_barrier_init();
   }
-  if (warp == 9) {
+  if (warp == kSoftmaxWarps + 1) {
     tc::tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), kTmemCols);
     tc::tmem_relinquish();
   }
@@ -144,9 +204,9 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
   const uint32_t dbg_mode =
       (kDebug && debug != nullptr) ? reinterpret_cast<const uint32_t*>(debug)[32768 + 3 * 64 * 8] : 0u;
 
-  if (warp >= 8) {
-    tc::reg_dealloc<96>();
-    if (warp == 8) {
+  if (warp >= kSoftmaxWarps) {
+    tc::reg_dealloc<kRegsOther>();
+    if (warp == kSoftmaxWarps) {
       // ================================ TMA producer (warp-wide, issue by one elected lane) ==========
       const bool lead = tc::elect_one();
       if (lead) {
@@ -199,7 +259,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           __syncwarp();
         }
       }
-    } else if (warp == 9) {
+    } else if (warp == kSoftmaxWarps + 1) {
       // ================================ MMA issuer (warp-wide, issue by one elected lane) ============
       // Measured with clock64 stamps (tools/trace_prefill.py): run by a single divergent lane, every
       // tcgen05.mma cost ~100-140 cycles of R2UR moves plus an ELECT/branch waterfall, i.e. the issue path,
@@ -210,9 +270,12 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
       uint32_t kv_base = 0;          // K/V tiles consumed by earlier items
       uint32_t q_uses[2] = {0, 0};   // items that used tile t (phase of q_full / o_empty)
       uint32_t p_cnt[2] = {0, 0};    // P tiles consumed per query tile (phase of p_full)
+      int item_k = 0;
       for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
         const Item it = decode_item(p, w, num_pairs, batch);
         if (!it.live) continue;
+        const bool tri = kDebug && lead && debug != nullptr && blockIdx.x == 0;
+        if (tri) item_stamp(debug, item_k, 5);
         auto issue_qk = [&](int t, int j) {
           const uint32_t kv = kv_base + static_cast<uint32_t>(j);
           const uint32_t st = kv % kStages;
@@ -282,6 +345,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         };
         for (int t = 0; t < 2; ++t)
           if (it.n_t[t] > 0) issue_qk(t, 0);
+        if (tri) item_stamp(debug, item_k, 6);
         const bool tr = kDebug && lead && debug != nullptr && blockIdx.x == 0 && w == static_cast<int>(blockIdx.x);
         for (int j = 0; j < it.n_tiles; ++j) {
           if (tr) trace_stamp(debug, 0, j, 0);
@@ -296,6 +360,8 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           if (j + 1 < it.n_t[1]) issue_qk(1, j + 1);
           if (tr) trace_stamp(debug, 0, j, 4);
         }
+        if (tri) item_stamp(debug, item_k, 7);
+        ++item_k;
         kv_base += static_cast<uint32_t>(it.n_tiles);
         for (int t = 0; t < 2; ++t)
           if (it.n_t[t] > 0) ++q_uses[t];
@@ -303,13 +369,13 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     }
     __syncwarp();
   } else {
-    tc::reg_alloc<200>();
+    tc::reg_alloc<kRegsSoftmax>();
 #include "prefill_tcgen05_softmax.inl"
   }
 
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 9) tc::tmem_dealloc(tmem, kTmemCols);
+  if (warp == kSoftmaxWarps + 1) tc::tmem_dealloc(tmem, kTmemCols);
 }
 
 // ---- host: tensor maps ------------------------------------------------------------------------
@@ -344,8 +410,10 @@ bool make_map(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, 
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+constexpr int kDefaultEmu = 2;
 #ifdef NVLLM_TOOLS_BUILD
 float* g_debug = nullptr;
+int g_emu = -1;
 #endif
 
 }  // namespace
@@ -360,28 +428,38 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
   if (!make_map(&tq, p.q, static_cast<uint64_t>(p.num_q_heads) * kHeadDim, p.total_q, p.q_row_stride)) return NVLLM_OK;
   if (!make_map(&tk, p.k, kv_cols, p.total_k, p.k_row_stride)) return NVLLM_OK;
   if (!make_map(&tv, p.v, kv_cols, p.total_k, p.v_row_stride)) return NVLLM_OK;
-  static PerDeviceOnce configured;
-  cudaError_t e0 = once_per_device(configured, [] {
-    cudaError_t e = cudaFuncSetAttribute(prefill_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemBytes);
+  using Kernel = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const PrefillParams, const int,
+                          const int, float*);
+  Kernel kernel = prefill_tcgen05_kernel<false, kDefaultEmu>;
+  float* debug = nullptr;
 #ifdef NVLLM_TOOLS_BUILD
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(prefill_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  debug = g_debug;
+  switch (g_emu >= 0 ? g_emu : kDefaultEmu) {
+    case 0: kernel = debug ? prefill_tcgen05_kernel<true, 0> : prefill_tcgen05_kernel<false, 0>; break;
+    case 1: kernel = prefill_tcgen05_kernel<false, 1>; break;
+    case 2: kernel = prefill_tcgen05_kernel<false, 2>; break;
+    case 3: kernel = prefill_tcgen05_kernel<false, 3>; break;
+    case 4: kernel = prefill_tcgen05_kernel<false, 4>; break;
+    default: kernel = prefill_tcgen05_kernel<false, 5>; break;
+  }
+  if (debug && kernel != prefill_tcgen05_kernel<true, 0>) kernel = prefill_tcgen05_kernel<true, kDefaultEmu>;
 #endif
-    return e;
+  // (the attribute is per function and per device: set it on every launch of a tools build, once in the product)
+#ifndef NVLLM_TOOLS_BUILD
+  static PerDeviceOnce configured;
+  cudaError_t e0 = once_per_device(configured, [kernel] {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   });
+#else
+  cudaError_t e0 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+#endif
   if (e0 != cudaSuccess) return record_cuda_error(e0);
   const int num_pairs = (max_seqlen_q + 2 * TM - 1) / (2 * TM);
   const int64_t total = static_cast<int64_t>(num_pairs) * p.num_q_heads * batch;
   if (total > INT32_MAX) return NVLLM_ERR_UNSUPPORTED;
   const int sms = device_sm_count();
   const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);   // persistent: one CTA per SM
-#ifdef NVLLM_TOOLS_BUILD
-  if (g_debug)
-    prefill_tcgen05_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, g_debug);
-  else
-#endif
-    prefill_tcgen05_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, nullptr);
+  kernel<<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, debug);
   note_launch();
   *handled = true;
   return record_cuda_error(cudaGetLastError());
@@ -395,4 +473,5 @@ int prefill_tcgen05_error_fetch(unsigned int* code) { return record_cuda_error(t
 extern "C" void nvllm_varlen_prefill_set_debug_buffer(void* device_ptr) {
   nvllm::g_debug = static_cast<float*>(device_ptr);
 }
+extern "C" void nvllm_varlen_prefill_set_exp2_poly(int pairs_of_8) { nvllm::g_emu = pairs_of_8; }
 #endif

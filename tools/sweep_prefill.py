@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
-from nano_vllm_learn_b200 import ops  # noqa: E402
+from nano_vllm_learn_b200 import _lib, ops  # noqa: E402
 
 D, BLOCK = 128, 256
 
@@ -40,8 +40,12 @@ def main():
     ap.add_argument("--shape-idx", type=int, default=-1)
     ap.add_argument("--impls", default="tcgen05,mma.sync")
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--emu", default="", help="comma list of exp2-on-FMA settings of the tcgen05 kernel (pairs of 8; "
+                    "needs the tools library: python nano-vllm-learn_b200/build.py --tools)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
+    if args.emu:
+        _lib.load_tools()      # before anything loads the product library
     # (name, batch, Lq, cached, Hq, Hkv)
     shapes = [("bench.py step 16x1024 0.6B", 16, 1024, 0, 16, 8),
               ("C3 prefix 16x(512 new + 512 cached) 0.6B", 16, 512, 512, 16, 8),
@@ -83,6 +87,21 @@ def main():
             med, mn = timeit(f, args.iters)
             print(json.dumps(dict(shape=name, impl=label, us=round(med, 1), us_min=round(mn, 1),
                                   tflops=round(fl / med / 1e6, 1), gflop=round(fl / 1e9, 2))), flush=True)
+        if args.emu:
+            tl = _lib.load_tools()
+            ops.set_prefill_variant(1)
+            f = lambda: ops.flash_attn_varlen_func(q, k, v, lq, cu_q, lk, cu_k, softmax_scale=scale, block_table=tab, out=out)
+            base = None
+            for e in [int(x) for x in args.emu.split(",")]:
+                tl.nvllm_varlen_prefill_set_exp2_poly(e)
+                med, mn = timeit(f, args.iters)
+                res = f().float()
+                if base is None:
+                    base = res
+                print(json.dumps(dict(shape=name, impl="tcgen05", exp2_poly_pairs_of_8=e, us=round(med, 1), us_min=round(mn, 1),
+                                      tflops=round(fl / med / 1e6, 1),
+                                      max_abs_diff_vs_first=round((res - base).abs().max().item(), 6))), flush=True)
+            tl.nvllm_varlen_prefill_set_exp2_poly(-1)
         ops.set_prefill_variant(-1)
         if fa is not None:
             f = lambda: fa(q, k, v, max_seqlen_q=lq, cu_seqlens_q=cu_q, max_seqlen_k=lk, cu_seqlens_k=cu_k,
