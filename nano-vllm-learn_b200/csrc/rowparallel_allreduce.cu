@@ -24,7 +24,7 @@
 //   Hardware assumption, the one NCCL's LL protocol makes with the very same instructions (its storeLL / readLL are
 //   st/ld.volatile.global.v4.u32 over {data1, flag1, data2, flag2}): each naturally aligned 8-byte half of a 16-byte
 //   vector access is single-copy atomic over NVLink and in L2, so a half whose epoch matches carries that epoch's
-//   payload.  tests/test_gpu_rowparallel.py::test_ll_exchange_stress hammers it with randomised payloads.
+//   payload.  tests/test_gpu_rowparallel_worlds.py::test_ll_exchange_stress hammers it (worlds 2, 4, 8).
 //   These words live in a region of their own -- anchored at the END of each parity, while the fp32 inboxes and the
 //   two-shot result area of every other plan grow from its start, and nvllm_rowparallel_comm_layout sizes the buffer
 //   so the two never meet -- zeroed at allocation, so nothing but an older epoch can ever sit there.
