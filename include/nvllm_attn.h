@@ -322,6 +322,53 @@ NVLLM_API int nvllm_sample_tokens(int64_t* tokens_out, const void* logits,
 NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
 
 /* ------------------------------------------------------------------------
+ * (5b) vocabulary-parallel sampling (second half): the
+ *      sampler on each rank's OWN logits shard + a 16-byte-per-row exchange
+ *      over NVLink peer memory, instead of gathering [bs, vocab/tp] logits
+ *      from every rank to rank 0 over NCCL and concatenating them.
+ *      reference: nanovllm/layers/embed_head.py:66-70 (dist.gather +
+ *                 torch.cat in ParallelLMHead.forward), then
+ *                 nanovllm/layers/sampler.py:10-18 on rank 0 and the
+ *                 device->host read at engine/model_runner.py:311.
+ *
+ *   logits_shard [bs, vocab_shard] holds columns [vocab_offset, vocab_offset
+ *   + vocab_shard) of the full logits (vocab_offset % 4 == 0).  Each rank
+ *   reduces its shard to one (key, global index) pair per row -- Philox
+ *   counters use the GLOBAL element index, so the noise of an element does
+ *   not depend on how the vocabulary is split -- pushes the pair to every
+ *   peer as two 8-byte {payload, call epoch} words and takes the best of the
+ *   `world` pairs in torch.argmax order.  EVERY rank receives tokens_out
+ *   [bs], bit-identical to nvllm_sample_tokens on the concatenated logits
+ *   with the same (seed, offset) / the concatenated noise.  tokens_out may be
+ *   mapped pinned host memory.  noise_shard, if given, is this rank's
+ *   [bs, vocab_shard] slice.  temperatures: required on rank 0, which also
+ *   hands them to the peers through the exchange buffer; a rank > 0 may pass
+ *   NULL and then uses rank 0's (the reference's worker ranks never learn the
+ *   temperatures: engine/sequence.py:77-83 does not pickle them,
+ *   model_runner.py:309 prepares them on rank 0 only).
+ *   Communicator: one buffer of nvllm_sample_comm_bytes(world, max_bs) bytes
+ *   per rank from nvllm_tp_comm_alloc (zeroed), peers mapped as in (6);
+ *   comm_ptrs / comm_bytes / rank / world as in (6), the same comm_bytes on
+ *   every rank.  All ranks issue the same sequence of calls with the same bs;
+ *   calls on one communicator are stream-ordered (not concurrent), graph-
+ *   capturable, and need no host synchronisation between ranks.  A peer that
+ *   never arrives: timeout (default 20 s, nvllm_sample_sharded_set_timeout_ms)
+ *   -> error latch readable with nvllm_sample_sharded_poll_error (mapped host
+ *   word: 0 = none, else 1 + row) and nvllm_tp_comm_status.
+ * ---------------------------------------------------------------------- */
+NVLLM_API size_t nvllm_sample_comm_bytes(int32_t world, int32_t max_bs);
+NVLLM_API int nvllm_sample_tokens_sharded(int64_t* tokens_out, const void* logits_shard,
+                                int32_t logits_elem_bytes, int64_t logits_row_stride,
+                                const float* temperatures, const float* noise_shard,
+                                int64_t noise_row_stride, int32_t bs, int32_t vocab_shard,
+                                int32_t vocab_offset, uint64_t seed, uint64_t offset,
+                                void* workspace, size_t workspace_bytes,
+                                void* const* comm_ptrs, size_t comm_bytes,
+                                int32_t rank, int32_t world, void* stream);
+NVLLM_API int nvllm_sample_sharded_poll_error(uint32_t* error_out, int32_t clear);
+NVLLM_API int nvllm_sample_sharded_set_timeout_ms(int64_t timeout_ms);
+
+/* ------------------------------------------------------------------------
  * (6) fused RowParallelLinear (SURVEY §8f "next", rank 2): the o_proj /
  *     down_proj GEMM and the tensor-parallel all-reduce that follows it, in
  *     ONE launch per rank over NVLink peer memory.

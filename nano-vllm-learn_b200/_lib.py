@@ -42,6 +42,12 @@ SIGNATURES = {
     "nvllm_sample_tokens": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_uint64, c_uint64, c_void_p, c_size_t, c_void_p]),
     "nvllm_sample_workspace_bytes": (c_size_t, [c_int32]),
+    "nvllm_sample_comm_bytes": (c_size_t, [c_int32, c_int32]),
+    "nvllm_sample_tokens_sharded": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32,
+                                            c_int32, c_int32, c_uint64, c_uint64, c_void_p, c_size_t,
+                                            ctypes.POINTER(c_void_p), c_size_t, c_int32, c_int32, c_void_p]),
+    "nvllm_sample_sharded_poll_error": (c_int, [ctypes.POINTER(ctypes.c_uint32), c_int32]),
+    "nvllm_sample_sharded_set_timeout_ms": (c_int, [c_int64]),
     "nvllm_rowparallel_comm_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "nvllm_rowparallel_comm_layout": (c_int, [c_int32, c_int32, c_int32, c_int32, ctypes.POINTER(c_size_t),
                                               ctypes.POINTER(c_size_t), ctypes.POINTER(c_size_t)]),

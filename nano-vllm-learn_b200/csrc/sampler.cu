@@ -13,7 +13,19 @@
 // Grid (chunks, bs): a CTA reduces one chunk of one row to a (value, index) pair per criterion; the last CTA
 // of a row to arrive (self-resetting counter in the workspace, as in paged_decode.cu) merges the chunk
 // partials and writes the int64 token id.
+//
+// Vocabulary-parallel mode (nvllm_sample_tokens_sharded; SURVEY §8f rank 4, second half): under tensor parallelism
+// every rank holds logits[:, r*V/tp : (r+1)*V/tp] (ParallelLMHead, nanovllm/layers/embed_head.py:61-65).  The
+// reference gathers all shards on rank 0 over NCCL and concatenates them (embed_head.py:66-70: bs*V*2 bytes into
+// one GPU per step) before Sampler.forward runs there.  Here each rank reduces ITS shard to one (key, global index)
+// pair per row with the very same walk (Philox counters use the global element index, so the draw does not depend on
+// the sharding), and the row's finishing warp swaps pairs with the other ranks through NVLink peer memory as 8-byte
+// {payload, call epoch} words -- flag-in-data, no fence, no separate flag -- then takes the best of `world` pairs in
+// torch.argmax order.  16*(world-1) bytes per row cross NVLink instead of V*2*(world-1)/world; every rank ends up
+// with the token ids (the next step's input_ids never leave the devices), bit-identical to the unsharded kernel on
+// the concatenated logits.
 #include <limits.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -85,7 +97,44 @@ struct SampleParams {
   float4* partials;          // [bs][chunks] = (greedy value, greedy index, sample key, sample index)
   int vocab, chunk_elems, chunks;
   uint32_t seed_lo, seed_hi, off_lo, off_hi;
+  // vocabulary-parallel mode (world > 1)
+  int vocab_offset;          // global index of this shard's column 0 (multiple of 4)
+  int world, rank, bs, max_bs;
+  char* comm[8];             // every rank's exchange buffer as mapped here; comm[rank] is the local one
+  unsigned long long timeout_ns;
+  uint32_t* host_error;      // mapped pinned host word (may be null)
 };
+
+// ---- exchange buffer of the vocabulary-parallel mode ------------------------------------------------------------
+// [0, 4096): control words {epoch = calls completed, rows finished in the running call, error latch};
+// then [epoch parity][source rank][row] 16-byte slots {key bits, epoch, index, epoch}, then [epoch parity][row] 8-byte
+// words {temperature bits, epoch} written by rank 0.  A rank can be at most one
+// call ahead of a peer (it needs every peer's pair of call e to finish call e), so two parities suffice; the buffer
+// is zeroed at allocation and epochs start at 1, so a stale word never passes for a current one.
+constexpr size_t kXchgHeader = 4096;
+constexpr size_t kXchgMinBytes = 299008;   // nvllm_tp_comm_alloc's minimum (it also serves the fused all-reduce)
+struct XchgControl {
+  uint32_t epoch, rows_done, error;   // same word order as the fused all-reduce's control area (nvllm_tp_comm_status)
+};
+
+__device__ __forceinline__ unsigned long long sampler_globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void st_volatile_v2u(void* p, uint32_t a, uint32_t b) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};\n" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ uint2 ld_volatile_v2u(const void* p) {
+  uint2 r;
+  asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];\n" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_volatile_u32(const void* p) {
+  uint32_t r;
+  asm volatile("ld.volatile.global.u32 %0, [%1];\n" : "=r"(r) : "l"(p) : "memory");
+  return r;
+}
 
 template <typename T>
 __device__ __forceinline__ float to_f32(T x);
@@ -151,6 +200,42 @@ __device__ __forceinline__ float skip_threshold(float best_key, float temp) {
   return t - fabsf(t) * 9.5367431640625e-7f;
 }
 
+// Vocabulary-parallel merge of one row, run by the first warp of the row's finishing CTA.  Lane r talks to rank r:
+// it pushes this rank's (key, global index) into rank r's inbox slot [parity][this rank][row] and polls the local
+// slot [parity][r][row] until both 8-byte words carry this call's epoch.  Returns the best of all ranks in every lane.
+__device__ __forceinline__ Cand exchange_row(const SampleParams& p, int row, Cand mine, int lane) {
+  XchgControl* ctl = reinterpret_cast<XchgControl*>(p.comm[p.rank]);
+  const uint32_t epoch = ld_volatile_u32(&ctl->epoch) + 1u;
+  const size_t parity_off = kXchgHeader + static_cast<size_t>(epoch & 1u) * p.world * p.max_bs * 16;
+  Cand got = Cand{-INFINITY, INT_MAX};
+  if (lane == p.rank) {
+    got = mine;
+  } else if (lane < p.world) {
+    char* dst = p.comm[lane] + parity_off + (static_cast<size_t>(p.rank) * p.max_bs + row) * 16;
+    st_volatile_v2u(dst, __float_as_uint(mine.v), epoch);
+    st_volatile_v2u(dst + 8, static_cast<uint32_t>(mine.i), epoch);
+    const char* src = p.comm[p.rank] + parity_off + (static_cast<size_t>(lane) * p.max_bs + row) * 16;
+    const unsigned long long t0 = sampler_globaltimer_ns();
+    uint2 a, b;
+    for (uint32_t spins = 1;; ++spins) {
+      a = ld_volatile_v2u(src);
+      b = ld_volatile_v2u(src + 8);
+      if (a.y == epoch && b.y == epoch) break;
+      if ((spins & 1023u) == 0 && sampler_globaltimer_ns() - t0 > p.timeout_ns) {
+        // the peer never arrived: latch (device word + mapped host word) and go on with what is here
+        atomicCAS(&ctl->error, 0u, 1u + static_cast<uint32_t>(row));
+        if (p.host_error) *reinterpret_cast<volatile uint32_t*>(p.host_error) = 1u + static_cast<uint32_t>(row);
+        a.x = __float_as_uint(-INFINITY);
+        b.x = static_cast<uint32_t>(INT_MAX);
+        break;
+      }
+    }
+    got = Cand{__uint_as_float(a.x), static_cast<int>(b.x)};
+  }
+  warp_best(got);
+  return got;
+}
+
 constexpr int kUnroll = 4;   // 16-byte loads in flight per thread
 
 // kVec elements per thread per load: 8 bf16 or 4 fp32.
@@ -162,7 +247,37 @@ __global__ void __launch_bounds__(kSampleThreads, 4) sample_tokens_kernel(const 
   const int chunk = blockIdx.x;
   const int tid = threadIdx.x;
   const T* lrow = static_cast<const T*>(p.logits) + static_cast<int64_t>(row) * p.row_stride;
-  const float temp = __ldg(p.temperatures + row);
+  float temp;
+  if (p.world > 1) {
+    // Only rank 0 is sure to know the temperatures (the engine's worker ranks never see them: Sequence.__getstate__,
+    // nanovllm/engine/sequence.py:77-83, does not pickle them).  Rank 0 hands each row's value to the peers as one
+    // {temperature bits, call epoch} word; a rank called without temperatures waits for that word.
+    XchgControl* ctl = reinterpret_cast<XchgControl*>(p.comm[p.rank]);
+    const uint32_t epoch = ld_volatile_u32(&ctl->epoch) + 1u;
+    const size_t toff = kXchgHeader + 2 * static_cast<size_t>(p.world) * p.max_bs * 16 +
+                        (static_cast<size_t>(epoch & 1u) * p.max_bs + row) * 8;
+    if (p.temperatures) {
+      temp = __ldg(p.temperatures + row);
+      if (p.rank == 0 && chunk == 0 && tid > 0 && tid < p.world) st_volatile_v2u(p.comm[tid] + toff, __float_as_uint(temp), epoch);
+    } else {
+      const char* src = p.comm[p.rank] + toff;
+      const unsigned long long t0 = sampler_globaltimer_ns();
+      uint2 w;
+      for (uint32_t spins = 1;; ++spins) {
+        w = ld_volatile_v2u(src);
+        if (w.y == epoch) break;
+        if ((spins & 1023u) == 0 && sampler_globaltimer_ns() - t0 > p.timeout_ns) {
+          atomicCAS(&ctl->error, 0u, 1u + static_cast<uint32_t>(row));
+          if (p.host_error) *reinterpret_cast<volatile uint32_t*>(p.host_error) = 1u + static_cast<uint32_t>(row);
+          w.x = 0u;   // fall back to greedy
+          break;
+        }
+      }
+      temp = __uint_as_float(w.x);
+    }
+  } else {
+    temp = __ldg(p.temperatures + row);
+  }
   const bool sample = temp != 0.f;
   const float inv_t = __frcp_rn(temp);
   const float* nrow = p.noise ? p.noise + static_cast<int64_t>(row) * p.noise_row_stride : nullptr;
@@ -217,7 +332,8 @@ __global__ void __launch_bounds__(kSampleThreads, 4) sample_tokens_kernel(const 
 #pragma unroll
           for (int k = 0; k < kVec; k += 4) {
             const uint4 r = philox4x32_10(
-                make_uint4(static_cast<uint32_t>((i0 + k) >> 2), static_cast<uint32_t>(row), p.off_lo, p.off_hi), key);
+                make_uint4(static_cast<uint32_t>((p.vocab_offset + i0 + k) >> 2), static_cast<uint32_t>(row), p.off_lo,
+                           p.off_hi), key);
             e[k + 0] = exp1_from_bits(r.x);
             e[k + 1] = exp1_from_bits(r.y);
             e[k + 2] = exp1_from_bits(r.z);
@@ -274,10 +390,26 @@ __global__ void __launch_bounds__(kSampleThreads, 4) sample_tokens_kernel(const 
   }
   warp_best(g);
   warp_best(s);
+  Cand f = sample ? s : g;   // every lane holds the row's winner (xor butterfly); .i is the index inside this shard
+  if (p.world > 1) {
+    if (f.i != INT_MAX) f.i += p.vocab_offset;
+    f = exchange_row(p, row, f, tid);
+  }
   if (tid == 0) {
-    int tok = sample ? s.i : g.i;
+    int tok = f.i;
     if (tok == INT_MAX) tok = 0;   // a row whose every key is -inf: torch.argmax answers 0
     p.tokens[row] = static_cast<int64_t>(tok);
+    if (p.world > 1) {
+      // the call is complete on this rank once every row has swapped: the last row advances the call epoch
+      XchgControl* ctl = reinterpret_cast<XchgControl*>(p.comm[p.rank]);
+      const uint32_t epoch = ld_volatile_u32(&ctl->epoch) + 1u;
+      __threadfence();
+      if (atomicAdd(&ctl->rows_done, 1u) == static_cast<uint32_t>(p.bs) - 1u) {
+        ctl->rows_done = 0;
+        __threadfence();
+        *reinterpret_cast<volatile uint32_t*>(&ctl->epoch) = epoch;
+      }
+    }
   }
 }
 
@@ -290,16 +422,66 @@ extern "C" size_t nvllm_sample_workspace_bytes(int32_t bs) {
   return nvllm::kCounterBytes + static_cast<size_t>(bs) * nvllm::kMaxChunks * sizeof(float4);
 }
 
-extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int32_t logits_elem_bytes,
-                                   int64_t logits_row_stride, const float* temperatures, const float* noise,
-                                   int64_t noise_row_stride, int32_t bs, int32_t vocab, uint64_t seed,
-                                   uint64_t offset, void* workspace, size_t workspace_bytes, void* stream) {
-  using namespace nvllm;
+namespace nvllm {
+namespace {
+
+unsigned long long g_sample_timeout_ns = 20ull * 1000 * 1000 * 1000;
+
+// mapped pinned host word: the timeout latch of the vocabulary-parallel exchange, readable without a CUDA call
+uint32_t* sampler_host_error_word() {
+  static uint32_t* word = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      memset(q, 0, 64);
+      word = static_cast<uint32_t*>(q);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return word;
+}
+
+int launch_sampler(int64_t* tokens_out, const void* logits, int32_t logits_elem_bytes, int64_t logits_row_stride,
+                   const float* temperatures, const float* noise, int64_t noise_row_stride, int32_t bs, int32_t vocab,
+                   int32_t vocab_offset, uint64_t seed, uint64_t offset, void* workspace, size_t workspace_bytes,
+                   void* const* comm_ptrs, size_t comm_bytes, int32_t rank, int32_t world, void* stream) {
   if (bs == 0) return NVLLM_OK;
-  if (!tokens_out || !logits || !temperatures || bs < 0 || vocab <= 0 || logits_row_stride < vocab) return NVLLM_ERR_BAD_ARG;
+  if (!tokens_out || !logits || bs < 0 || vocab <= 0 || logits_row_stride < vocab) return NVLLM_ERR_BAD_ARG;
+  if (!temperatures && !(world > 1 && rank > 0)) return NVLLM_ERR_BAD_ARG;   // only worker ranks may wait for rank 0's
   if (logits_elem_bytes != 2 && logits_elem_bytes != 4) return NVLLM_ERR_UNSUPPORTED;
   if (static_cast<size_t>(bs) * sizeof(int) > kCounterBytes) return NVLLM_ERR_UNSUPPORTED;
   if (!workspace || workspace_bytes < nvllm_sample_workspace_bytes(bs) || !aligned16(workspace)) return NVLLM_ERR_WORKSPACE;
+
+  SampleParams p = {};
+  p.world = 1;
+  if (world > 1) {
+    if (world > 8 || rank < 0 || rank >= world || !comm_ptrs || vocab_offset < 0) return NVLLM_ERR_BAD_ARG;
+    if (vocab_offset % 4 != 0) return NVLLM_ERR_UNSUPPORTED;   // Philox blocks cover 4 consecutive GLOBAL elements
+    if (static_cast<int64_t>(vocab_offset) + vocab > INT_MAX - 1) return NVLLM_ERR_UNSUPPORTED;
+    // rows per parity this buffer holds: every rank must pass the same comm_bytes (the slot stride derives from it)
+    if (comm_bytes < kXchgHeader) return NVLLM_ERR_WORKSPACE;
+    const size_t max_bs = (comm_bytes - kXchgHeader) / (2 * static_cast<size_t>(world) * 16 + 16);
+    if (max_bs < static_cast<size_t>(bs)) return NVLLM_ERR_WORKSPACE;
+    p.max_bs = static_cast<int>(max_bs > 4096 ? 4096 : max_bs);
+    for (int r = 0; r < world; ++r) {
+      if (!comm_ptrs[r] || !aligned16(comm_ptrs[r])) return NVLLM_ERR_BAD_ARG;
+      p.comm[r] = static_cast<char*>(comm_ptrs[r]);
+    }
+    p.world = world;
+    p.rank = rank;
+    p.vocab_offset = vocab_offset;
+    p.timeout_ns = g_sample_timeout_ns;
+    p.host_error = nullptr;
+    if (uint32_t* hw = sampler_host_error_word()) {
+      void* dp = nullptr;
+      if (cudaHostGetDevicePointer(&dp, hw, 0) == cudaSuccess) p.host_error = static_cast<uint32_t*>(dp);
+      else cudaGetLastError();
+    }
+  }
+  p.bs = bs;
 
   const int sms = device_sm_count();
   const int vec = 16 / logits_elem_bytes;
@@ -311,7 +493,6 @@ extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int3
   chunk_elems = (chunk_elems + vec - 1) / vec * vec;
   chunks = (vocab + chunk_elems - 1) / chunk_elems;
 
-  SampleParams p;
   p.logits = logits;
   p.row_stride = logits_row_stride;
   p.temperatures = temperatures;
@@ -340,4 +521,48 @@ extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int3
   }
   note_launch();
   return record_cuda_error(cudaGetLastError());
+}
+
+}  // namespace
+}  // namespace nvllm
+
+extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int32_t logits_elem_bytes,
+                                   int64_t logits_row_stride, const float* temperatures, const float* noise,
+                                   int64_t noise_row_stride, int32_t bs, int32_t vocab, uint64_t seed,
+                                   uint64_t offset, void* workspace, size_t workspace_bytes, void* stream) {
+  return nvllm::launch_sampler(tokens_out, logits, logits_elem_bytes, logits_row_stride, temperatures, noise,
+                               noise_row_stride, bs, vocab, 0, seed, offset, workspace, workspace_bytes, nullptr, 0, 0, 1,
+                               stream);
+}
+
+extern "C" size_t nvllm_sample_comm_bytes(int32_t world, int32_t max_bs) {
+  if (world < 2 || world > 8 || max_bs <= 0 || max_bs > 4096) return 0;
+  const size_t need = nvllm::kXchgHeader + (2 * static_cast<size_t>(world) * 16 + 16) * max_bs;
+  return need < nvllm::kXchgMinBytes ? nvllm::kXchgMinBytes : need;
+}
+
+extern "C" int nvllm_sample_tokens_sharded(int64_t* tokens_out, const void* logits_shard, int32_t logits_elem_bytes,
+                                           int64_t logits_row_stride, const float* temperatures,
+                                           const float* noise_shard, int64_t noise_row_stride, int32_t bs,
+                                           int32_t vocab_shard, int32_t vocab_offset, uint64_t seed, uint64_t offset,
+                                           void* workspace, size_t workspace_bytes, void* const* comm_ptrs,
+                                           size_t comm_bytes, int32_t rank, int32_t world, void* stream) {
+  if (world < 2) return NVLLM_ERR_BAD_ARG;
+  return nvllm::launch_sampler(tokens_out, logits_shard, logits_elem_bytes, logits_row_stride, temperatures, noise_shard,
+                               noise_row_stride, bs, vocab_shard, vocab_offset, seed, offset, workspace, workspace_bytes,
+                               comm_ptrs, comm_bytes, rank, world, stream);
+}
+
+extern "C" int nvllm_sample_sharded_poll_error(uint32_t* error_out, int32_t clear) {
+  if (!error_out) return NVLLM_ERR_BAD_ARG;
+  uint32_t* w = nvllm::sampler_host_error_word();
+  *error_out = w ? *reinterpret_cast<volatile uint32_t*>(w) : 0u;
+  if (w && clear) *reinterpret_cast<volatile uint32_t*>(w) = 0u;
+  return NVLLM_OK;
+}
+
+extern "C" int nvllm_sample_sharded_set_timeout_ms(int64_t timeout_ms) {
+  if (timeout_ms <= 0) return NVLLM_ERR_BAD_ARG;
+  nvllm::g_sample_timeout_ns = static_cast<unsigned long long>(timeout_ms) * 1000000ull;
+  return NVLLM_OK;
 }

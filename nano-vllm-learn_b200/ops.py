@@ -255,7 +255,7 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
 
 
 # Sampler workspace (arrival counters + chunk partials), one per device, zero-filled once.
-_SAMPLE_WS: dict[int, torch.Tensor] = {}
+_SAMPLE_WS: dict = {}
 
 
 def sample_tokens(logits: torch.Tensor, temperatures: torch.Tensor, noise: Optional[torch.Tensor] = None,
@@ -275,17 +275,62 @@ def sample_tokens(logits: torch.Tensor, temperatures: torch.Tensor, noise: Optio
     if bs == 0:
         return out
     idx = logits.device.index if logits.device.index is not None else torch.cuda.current_device()
-    need = int(lib.nvllm_sample_workspace_bytes(bs))
-    ws = _SAMPLE_WS.get(idx)
-    if ws is None or ws.numel() < need:
-        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=logits.device)
-        _SAMPLE_WS[idx] = ws
+    ws = _sample_workspace(logits.device, bs, idx)
     st = lib.nvllm_sample_tokens(out.data_ptr(), logits.data_ptr(), logits.element_size(), logits.stride(0),
                                  temperatures.data_ptr(), noise.data_ptr() if noise is not None else None,
                                  noise.stride(0) if noise is not None else 0, bs, vocab,
                                  seed & 0xFFFFFFFFFFFFFFFF, offset & 0xFFFFFFFFFFFFFFFF, ws.data_ptr(), ws.numel(),
                                  _stream())
     _lib.check(st, "sample_tokens")
+    return out
+
+
+def _sample_workspace(device: torch.device, bs: int, key) -> torch.Tensor:
+    need = int(_lib.load().nvllm_sample_workspace_bytes(bs))
+    ws = _SAMPLE_WS.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=device)
+        _SAMPLE_WS[key] = ws
+    return ws
+
+
+def sample_tokens_sharded(logits_shard: torch.Tensor, temperatures: Optional[torch.Tensor], vocab_offset: int, comm,
+                          noise: Optional[torch.Tensor] = None, seed: int = 0, offset: int = 0,
+                          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Vocabulary-parallel Sampler: replaces the logits gather of ParallelLMHead.forward
+    (nanovllm/layers/embed_head.py:66-70) + Sampler.forward on rank 0 (nanovllm/layers/sampler.py:10-18).
+    `logits_shard` [bs, vocab/tp] are this rank's columns [vocab_offset, vocab_offset + vocab/tp) of the full logits;
+    `comm` is a TPComm sized with sampler_cuda.comm_bytes().  Every rank gets the int64 token ids [bs], equal to
+    sample_tokens() on the concatenated logits.  `out` may be a pinned host tensor (written through its mapping).
+    `temperatures` may be None on ranks > 0: rank 0's are used (it hands them over inside the kernel)."""
+    lib = _lib.load()
+    _require_cuda(logits_shard, temperatures, noise)
+    assert logits_shard.dim() == 2 and logits_shard.stride(1) == 1
+    assert logits_shard.dtype in (torch.bfloat16, torch.float32)
+    bs, vocab = logits_shard.shape
+    if temperatures is None:
+        assert comm.rank > 0, "rank 0 must supply the temperatures"
+    else:
+        assert temperatures.dtype == torch.float32 and temperatures.numel() == bs and temperatures.is_contiguous()
+    if noise is not None:
+        assert noise.dtype == torch.float32 and noise.shape == logits_shard.shape and noise.stride(1) == 1
+    if out is None:
+        out = torch.empty(bs, dtype=torch.int64, device=logits_shard.device)
+    else:
+        assert out.dtype == torch.int64 and out.numel() >= bs and out.is_contiguous() and (out.is_cuda or out.is_pinned())
+    if bs == 0:
+        return out
+    idx = logits_shard.device.index if logits_shard.device.index is not None else torch.cuda.current_device()
+    # one workspace per (device, communicator): ranks sharing a device (loop-back tests) launch concurrently
+    ws = _sample_workspace(logits_shard.device, bs, (idx, comm.local_ptr))
+    st = lib.nvllm_sample_tokens_sharded(out.data_ptr(), logits_shard.data_ptr(), logits_shard.element_size(),
+                                         logits_shard.stride(0),
+                                         temperatures.data_ptr() if temperatures is not None else None,
+                                         noise.data_ptr() if noise is not None else None,
+                                         noise.stride(0) if noise is not None else 0, bs, vocab, vocab_offset,
+                                         seed & 0xFFFFFFFFFFFFFFFF, offset & 0xFFFFFFFFFFFFFFFF, ws.data_ptr(),
+                                         ws.numel(), comm.ptr_array, comm.nbytes, comm.rank, comm.world, _stream())
+    _lib.check(st, "sample_tokens_sharded")
     return out
 
 

@@ -183,6 +183,31 @@ def make_sampler_case(name: str):
     return dict(logits=logits, temperatures=torch.tensor(temps, dtype=torch.float32), noise_seed=1000 + seed)
 
 
+# ---- vocabulary-parallel lm_head + sampler (second half) -----------------------------------
+# name -> (seed, tokens in x, hidden, vocab, world, temperatures per sampled row, prefill cu_seqlens_q or None)
+LM_HEAD_CASES = {
+    "vp_decode_tp2": (50, 6, 64, 4096, 2, [0.0, 0.0, 0.8, 1.0, 0.0, 0.5], None),
+    "vp_decode_tp4": (51, 5, 128, 2048, 4, [0.0, 0.7, 0.0, 1.2, 0.0], None),
+    "vp_prefill_tp2": (52, 11, 64, 1024, 2, [0.0, 0.9, 0.0], [0, 4, 5, 11]),     # last token of 3 sequences
+    "vp_greedy_tp8": (53, 4, 32, 1024, 8, [0.0, 0.0, 0.0, 0.0], None),
+}
+
+
+def make_lm_head_case(name: str):
+    """Hidden states + an lm_head weight; rows 0 and 1 of the weight matrix get duplicates in OTHER shards so that
+    exact logit ties across ranks occur (the lowest global index must win)."""
+    seed, n, hidden, vocab, world, temps, cu = LM_HEAD_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, hidden, generator=g).to(torch.bfloat16)
+    w = (torch.randn(vocab, hidden, generator=g) * (hidden ** -0.5)).to(torch.bfloat16)
+    # make the greedy winner of row 0 appear again in the last shard (same weight row -> identical logit)
+    logits0 = (x[0 if cu is None else cu[1] - 1].float() @ w.float().T)
+    top = int(logits0.argmax())
+    w[vocab - 3] = w[top]
+    return dict(x=x, weight=w, world=world, temperatures=torch.tensor(temps, dtype=torch.float32),
+                cu_seqlens_q=None if cu is None else torch.tensor(cu, dtype=torch.int32), noise_seed=2000 + seed)
+
+
 # ---- fused RowParallelLinear (SURVEY §8f rank 2) -------------------------------------------------------------
 # name -> (seed, n_tokens, in_features (all ranks), out_features, world, bias)
 ROWPARALLEL_CASES = {

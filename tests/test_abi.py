@@ -155,3 +155,32 @@ def test_ops_refuse_cpu_tensors(lib):
     cache = torch.zeros(1, 256, 2, 128, dtype=torch.bfloat16)
     with pytest.raises(RuntimeError):
         ops.store_kvcache(k, k, cache, cache, torch.zeros(2, dtype=torch.int32))
+
+
+def test_sharded_sampler_host_arithmetic_without_gpu(lib):
+    # exchange buffer: header + (2 parities x world x 16 B pairs + 2 x 8 B temperature words) per row, never below
+    # nvllm_tp_comm_alloc's minimum
+    assert lib.nvllm_sample_comm_bytes(1, 64) == 0 and lib.nvllm_sample_comm_bytes(9, 64) == 0
+    assert lib.nvllm_sample_comm_bytes(2, 0) == 0 and lib.nvllm_sample_comm_bytes(2, 4097) == 0
+    assert lib.nvllm_sample_comm_bytes(2, 512) == 299008
+    assert lib.nvllm_sample_comm_bytes(8, 4096) == 4096 + (2 * 8 * 16 + 16) * 4096
+    ptrs = (ctypes.c_void_p * 2)(16, 32)
+    # world < 2, bs == 0 no-op, rank out of range, rank 0 without temperatures, offset not a multiple of 4
+    base = dict(out=16, logits=16, eb=2, stride=1024, temps=16, noise=None, ns=0, bs=2, vocab=1024, off=0, ws=16, wsb=1 << 20,
+                comm=ptrs, cb=299008, rank=0, world=2)
+
+    def call(**kw):
+        a = dict(base, **kw)
+        return lib.nvllm_sample_tokens_sharded(a["out"], a["logits"], a["eb"], a["stride"], a["temps"], a["noise"], a["ns"],
+                                               a["bs"], a["vocab"], a["off"], 0, 0, a["ws"], a["wsb"], a["comm"], a["cb"],
+                                               a["rank"], a["world"], None)
+    assert call(world=1) == 1
+    assert call(bs=0) == 0
+    assert call(rank=2) == 1
+    assert call(temps=None) == 1
+    assert call(off=1022) == 2
+    assert call(cb=1024) == 5
+    assert call(bs=4096, cb=299008) == 5          # buffer holds (299008 - 4096) / 80 = 3686 rows
+    err = ctypes.c_uint32(7)
+    assert lib.nvllm_sample_sharded_poll_error(ctypes.byref(err), 0) in (0, 4)   # no device: pinned alloc may be refused
+    assert lib.nvllm_sample_sharded_set_timeout_ms(0) == 1

@@ -1,4 +1,4 @@
-"""The reference-side binding (INTEGRATION.md edits A1-A7, tools/make_integration.py) applies to the UNMODIFIED
+"""The reference-side binding (INTEGRATION.md edits A1-A8, tools/make_integration.py) applies to the UNMODIFIED
 reference: every anchored replacement matches exactly once, the edited files still compile, and nothing outside the
 documented files changes -- so `attn_backend="flash"` on the edited copy is the reference's stock code path.
 Runs where the reference install (baseline/_ref) or /root/reference exists; no GPU, nothing is imported from the copy.
@@ -36,7 +36,7 @@ def test_every_edit_applies_once_and_compiles(edited):
     src, dst, mi = edited
     touched = {rel for rel, _, _ in mi.EDITS}
     assert touched == {"nanovllm/config.py", "nanovllm/models/qwen3.py", "nanovllm/engine/model_runner.py",
-                       "nanovllm/layers/linear.py"}
+                       "nanovllm/layers/linear.py", "nanovllm/layers/embed_head.py"}
     for rel in sorted(touched) + ["nanovllm/layers/attention_cuda.py"]:
         py_compile.compile(os.path.join(dst, rel), doraise=True)
     for rel, old, new in mi.EDITS:

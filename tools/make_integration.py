@@ -3,7 +3,7 @@
     python tools/make_integration.py [--src baseline/_ref] [--dst /tmp/nvllm_integration/nanovllm_cuda]
 
 Copies `<src>/nanovllm` to `<dst>/nanovllm` (under the system temp directory by default, never inside the repository) and applies exactly the
-edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5/A6/A7), plus two environment-compat
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5-A8), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
 anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
@@ -63,6 +63,21 @@ EDITS = [
      '        from nano_vllm_learn_b200 import rowparallel_cuda as _fused_rowparallel   # A7: only with the cuda backend\n'
      '        _fused_rowparallel.configure(attn_backend == "cuda")\n'
      '        self.model = Qwen3ForCausalLM(hf_config)\n'),
+    # ---- A8 (second half; optional: NVLLM_VOCAB_PARALLEL_SAMPLER=0 keeps dist.gather + rank-0 sampling):
+    #      vocabulary-parallel sampling -- ParallelLMHead keeps its logits shard (nanovllm/layers/embed_head.py:66-70),
+    #      ModelRunner.run samples on every rank and swaps 16 bytes per row over NVLink (nanovllm/engine/model_runner.py:306-313)
+    ("nanovllm/layers/embed_head.py", None,
+     '\n\n# --- cuda backend: vocabulary-parallel sampling (no logits gather)\n'
+     'from nano_vllm_learn_b200.sampler_cuda import install_lm_head as _install_vocab_parallel_head\n'
+     '_install_vocab_parallel_head(ParallelLMHead)\n'),
+    ("nanovllm/engine/model_runner.py", None,
+     'from nano_vllm_learn_b200.sampler_cuda import install_runner as _install_vocab_parallel_run\n'
+     '_install_vocab_parallel_run(ModelRunner, reset_context)\n'),
+    ("nanovllm/engine/model_runner.py",
+     '        load_model(self.model, config.model)\n',
+     '        load_model(self.model, config.model)\n'
+     '        from nano_vllm_learn_b200 import sampler_cuda as _vocab_parallel   # A8: only with the cuda backend\n'
+     '        _vocab_parallel.configure(attn_backend == "cuda")\n'),
     # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
     ("nanovllm/config.py",
      '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',
