@@ -351,6 +351,13 @@ def run_cuda(args):
         except Exception as e:   # a comparator leg must not take the headline line down with it
             fused = {"failed": f"{type(e).__name__}: {e}"[:300]}
 
+    vp_sampler = None
+    if dist is not None and not args.no_fused_allreduce:
+        try:
+            vp_sampler = run_vocab_parallel_sampler(args, dev, rank, world, ops, dist)
+        except Exception as e:
+            vp_sampler = {"failed": f"{type(e).__name__}: {e}"[:300]}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, sample_bs=args.cpu_sample_bs, iters=None)
@@ -384,7 +391,8 @@ def run_cuda(args):
                        "timing": "CUDA events on the launch stream, max over ranks"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
             "cpu_baseline": cpu, "vs_flash": vs_flash, "tp_strong": tp_strong, "long_ctx": long_ctx,
-            "prefill": prefill, "fused_allreduce": fused, "tp_e2e": tp_e2e}
+            "prefill": prefill, "fused_allreduce": fused, "vocab_parallel_sampler": vp_sampler,
+            "tp_e2e": tp_e2e}
     print(json.dumps(line), flush=True)
 
 
@@ -775,6 +783,95 @@ def run_fused_allreduce(args, dev, rank, world, ops, dist):
             "timing": f"CUDA-graph chains of {chain} calls x {iters} replays, max over ranks", "rows": rows}
 
 
+def run_vocab_parallel_sampler(args, dev, rank, world, ops, dist):
+    """SURVEY §8f rank 4 (second half), N > 1 only: vocabulary-parallel sampling -- every rank reduces ITS
+    [bs, vocab/N] logits shard and swaps one 16-byte pair per row over NVLink peer memory inside the sampler kernel --
+    beside the reference's path: dist.gather of the shards to rank 0 + torch.cat (nanovllm/layers/embed_head.py:66-70)
+    + Sampler.forward on rank 0 (nanovllm/layers/sampler.py:10-18; the eager reference module, and this repo's fused
+    one-launch sampler as a second comparator).  Parity on the box first (greedy + sampled rows with the same injected
+    Exp(1) draw: tokens equal on EVERY rank to rank 0's reference tokens), then device time per call, CUDA events,
+    max over ranks."""
+    from nano_vllm_learn_b200 import sampler_cuda
+    from nano_vllm_learn_b200.rowparallel_cuda import TPComm
+    vocab = 151936
+    if vocab % (4 * world):
+        return {"skipped": f"vocab {vocab} not divisible by 4*{world}"}
+    shard = vocab // world
+    _lib = __import__("nano_vllm_learn_b200._lib", fromlist=["x"])
+    _lib.check(_lib.load().nvllm_sample_sharded_set_timeout_ms(5000), "set_timeout")
+    comm = TPComm.from_process_group(sampler_cuda.comm_bytes(world))
+    ref_cls = _reference_sampler_class()
+    rows, all_ok = [], True
+    call = 0
+    for bs in (1, 16, 64, 256):
+        gen = torch.Generator(device=dev).manual_seed(9000 + bs)          # same full tensors on every rank
+        logits = (torch.empty(bs, vocab, dtype=torch.float32, device=dev).normal_(generator=gen) * 3).to(torch.bfloat16)
+        temps = torch.tensor([0.0 if i % 2 == 0 else 0.8 for i in range(bs)], dtype=torch.float32, device=dev)
+        noise = torch.empty(bs, vocab, dtype=torch.float32, device=dev).exponential_(1, generator=gen)
+        mine = logits[:, rank * shard:(rank + 1) * shard].contiguous()
+        nz = noise[:, rank * shard:(rank + 1) * shard].contiguous()
+        tok = ops.sample_tokens_sharded(mine, temps if rank == 0 else None, rank * shard, comm, noise=nz)
+        # the reference path on the same data: gather to rank 0, cat, sample there
+        parts = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
+        dist.gather(mine, parts, 0)
+        want = torch.zeros(bs, dtype=torch.int64, device=dev)
+        if rank == 0:
+            full = torch.cat(parts, -1)
+            # sampler.py:10-18 line by line in torch, the exponential_ draw replaced by the injected one
+            lf = full.to(torch.float)
+            probs = torch.softmax(lf / temps.unsqueeze(1), dim=-1, dtype=torch.float)
+            want = torch.where(temps == 0, lf.argmax(-1), probs.div_(noise + 1e-10).argmax(-1))
+            if ref_cls is not None:                              # greedy rows against the reference class itself
+                rt = ref_cls()(full.clone(), temps)
+                want = torch.where(temps == 0, rt, want)
+        dist.broadcast(want, 0)
+        torch.cuda.synchronize()
+        flag = torch.tensor([1 if (torch.equal(tok, want) and sampler_cuda.poll_error() == 0) else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = bool(flag.item())
+        all_ok = all_ok and ok
+
+        def timed(fn, iters=30):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(iters):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([a.elapsed_time(b) * 1e3 / iters], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return round(float(t.item()), 2)
+
+        def sharded():
+            ops.sample_tokens_sharded(mine, temps if rank == 0 else None, rank * shard, comm, seed=1, offset=bs)
+
+        def gather_then(sample):
+            def fn():
+                dist.gather(mine, parts, 0)
+                if rank == 0:
+                    sample(torch.cat(parts, -1), temps)
+            return fn
+        row = {"bs": bs, "vocab": vocab, "parity_ok": ok, "gather_bytes_to_rank0": bs * shard * 2 * (world - 1),
+               "exchange_bytes_per_rank": bs * 16 * (world - 1)}
+        if ok:
+            row["us_vocab_parallel"] = timed(sharded)
+            row["us_gather_fused_sampler"] = timed(gather_then(lambda l, t: ops.sample_tokens(l, t, seed=1, offset=bs)))
+            if ref_cls is not None:
+                ref = ref_cls()
+                row["us_gather_reference_sampler"] = timed(gather_then(lambda l, t: ref(l, t)), iters=10)
+                row["speedup_vs_reference"] = round(row["us_gather_reference_sampler"] / row["us_vocab_parallel"], 2)
+        rows.append(row)
+    torch.cuda.synchronize()
+    dist.barrier()
+    return {"parity_ok": all_ok, "world": world, "transport": comm.how, "timeout_latch": sampler_cuda.poll_error(),
+            "timing": "eager launches back to back (the sampler is outside the engine's CUDA graphs), CUDA events, "
+                      "max over ranks", "rows": rows}
+
+
 def run_tp_e2e(args, world):
     """The metric BASELINE.json names beside the op-level one: bench_my decode tok/s of the reference ENGINE at
     tensor_parallel_size = N (its own spawned ranks, NCCL, scheduler, CUDA graphs), `flash` backend vs `cuda` backend
@@ -839,6 +936,19 @@ def run_tp_e2e(args, world):
             if k2 != "flash":
                 out[f"{k2}_over_flash"] = round(v / good["flash"], 3)
     return out
+
+
+def _reference_sampler_class():
+    """The reference's UNMODIFIED Sampler class (nanovllm/layers/sampler.py), loaded from its source file in
+    baseline/_ref so that the nanovllm package (engine, flash-attn, triton) is not imported; None if absent."""
+    import importlib.util
+    path = os.path.join(ROOT, "baseline", "_ref", "nanovllm", "layers", "sampler.py")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location("_ref_sampler_bench", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.Sampler
 
 
 # --------------------------------------------------------------------------------------- CPU arms

@@ -288,6 +288,34 @@ NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
                                     int64_t capacity);
 
 /* ------------------------------------------------------------------------
+ * (4b) prepare_decode ON THE DEVICE: advance the decode
+ *      metadata of an unchanged running batch by one generated token, in
+ *      place, in the buffers the captured CUDA graph reads.
+ *      reference: nanovllm/engine/model_runner.py:244-269 (prepare_decode:
+ *                 Python lists over seqs + 5 pinned tensors + 5 H2D copies per
+ *                 token), :160-169 (prepare_block_tables),
+ *                 engine/block_manager.py:134-159 (may_append opens a block
+ *                 when len % block_size == 1)
+ *
+ *   for b < bs:  block_tables[patch_rows[i], patch_cols[i]] = patch_vals[i]
+ *                input_ids[b]    = sampled_tokens[b]   (sampler output, device)
+ *                context_lens[b] += 1;  positions[b] = context_lens[b]  (sic)
+ *                slot_mapping[b] = block_tables[b, (len-1)/block_size]
+ *                                  * block_size + (len-1) % block_size
+ *   patch_* are HOST arrays of n_patch <= nvllm_advance_decode_state_max_patches()
+ *   entries (the blocks may_append opened for this step), passed to the kernel
+ *   by value: no host-to-device copy.  Everything else is device memory.
+ * ---------------------------------------------------------------------- */
+NVLLM_API int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions,
+                               int32_t* slot_mapping, int32_t* context_lens,
+                               int32_t* block_tables, int64_t table_row_stride,
+                               const int64_t* sampled_tokens, int32_t bs,
+                               int32_t block_size, const int32_t* patch_rows,
+                               const int32_t* patch_cols, const int32_t* patch_vals,
+                               int32_t n_patch, void* stream);
+NVLLM_API int32_t nvllm_advance_decode_state_max_patches(void);
+
+/* ------------------------------------------------------------------------
  * (5) fused token sampler (SURVEY §8f "next", rank 4): one launch for the
  *     whole of Sampler.forward.
  *     reference: nanovllm/layers/sampler.py:10-18, called from
@@ -339,8 +367,10 @@ NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
  *   peer as two 8-byte {payload, call epoch} words and takes the best of the
  *   `world` pairs in torch.argmax order.  EVERY rank receives tokens_out
  *   [bs], bit-identical to nvllm_sample_tokens on the concatenated logits
- *   with the same (seed, offset) / the concatenated noise.  tokens_out may be
- *   mapped pinned host memory.  noise_shard, if given, is this rank's
+ *   with the same (seed, offset) / the concatenated noise.  tokens_out_host
+ *   (NULL or the device mapping of pinned host memory; with UVA that is the
+ *   host pointer itself) receives a second copy, so the host reads the ids
+ *   after a stream synchronise without a device-to-host copy.  noise_shard, if given, is this rank's
  *   [bs, vocab_shard] slice.  temperatures: required on rank 0, which also
  *   hands them to the peers through the exchange buffer; a rank > 0 may pass
  *   NULL and then uses rank 0's (the reference's worker ranks never learn the
@@ -357,7 +387,8 @@ NVLLM_API size_t nvllm_sample_workspace_bytes(int32_t bs);
  *   word: 0 = none, else 1 + row) and nvllm_tp_comm_status.
  * ---------------------------------------------------------------------- */
 NVLLM_API size_t nvllm_sample_comm_bytes(int32_t world, int32_t max_bs);
-NVLLM_API int nvllm_sample_tokens_sharded(int64_t* tokens_out, const void* logits_shard,
+NVLLM_API int nvllm_sample_tokens_sharded(int64_t* tokens_out, int64_t* tokens_out_host,
+                                const void* logits_shard,
                                 int32_t logits_elem_bytes, int64_t logits_row_stride,
                                 const float* temperatures, const float* noise_shard,
                                 int64_t noise_row_stride, int32_t bs, int32_t vocab_shard,

@@ -43,7 +43,7 @@ SIGNATURES = {
                                     c_uint64, c_uint64, c_void_p, c_size_t, c_void_p]),
     "nvllm_sample_workspace_bytes": (c_size_t, [c_int32]),
     "nvllm_sample_comm_bytes": (c_size_t, [c_int32, c_int32]),
-    "nvllm_sample_tokens_sharded": (c_int, [c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32,
+    "nvllm_sample_tokens_sharded": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_int64, c_void_p, c_void_p, c_int64, c_int32,
                                             c_int32, c_int32, c_uint64, c_uint64, c_void_p, c_size_t,
                                             ctypes.POINTER(c_void_p), c_size_t, c_int32, c_int32, c_void_p]),
     "nvllm_sample_sharded_poll_error": (c_int, [ctypes.POINTER(ctypes.c_uint32), c_int32]),
@@ -64,6 +64,9 @@ SIGNATURES = {
                                                    c_int32, c_int32, c_void_p]),
     "nvllm_rowparallel_plan": (c_int, [c_int32, c_int32, c_int32, c_int32, _P32, _P32, _P32]),
     "nvllm_rowparallel_set_plan": (c_int, [c_int32, c_int32, c_int32, c_int64]),
+    "nvllm_advance_decode_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int32,
+                                           c_int32, _P32, _P32, _P32, c_int32, c_void_p]),
+    "nvllm_advance_decode_state_max_patches": (c_int32, []),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),
 }

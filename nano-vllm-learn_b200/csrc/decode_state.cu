@@ -1,0 +1,89 @@
+// Device-side prepare_decode: advance the decode metadata of a running batch by one step IN the
+// buffers the captured CUDA graph reads, instead of rebuilding them on the host every generated token.
+//
+// Reference: ModelRunner.prepare_decode, nanovllm/engine/model_runner.py:244-269 -- per sequence
+//     input_ids  = seq.last_token                          (the token sampled in the previous step)
+//     positions  = len(seq)                                (sic: not len(seq) - 1, :251)
+//     context_lens = len(seq)
+//     slot       = seq.block_table[-1] * block_size + seq.last_block_num_tokens - 1   (:254-258, sequence.py:53-65)
+//     block_tables row = seq.block_table                   (prepare_block_tables, :160-169)
+// built as Python lists over `seqs`, five pinned tensors and five host-to-device copies per token.
+// Between two decode steps of the SAME batch every sequence grew by exactly one token (Scheduler.postprocess appends
+// the sampled id), so: ids <- the sampler's device output, positions += 1, context_lens += 1, slot recomputed from the
+// row's own table; the table itself only changes for the rows whose new length opened a block (BlockManager.may_append
+// allocates when len % block_size == 1, block_manager.py:134-159) -- those few (row, column, block id) entries travel
+// as kernel arguments.  One launch, no host-to-device copy, nothing read back.
+#include "common.cuh"
+
+namespace nvllm {
+namespace {
+
+constexpr int kMaxPatches = 16;
+
+struct AdvanceParams {
+  int64_t* input_ids;
+  int64_t* positions;
+  int32_t* slot_mapping;
+  int32_t* context_lens;
+  int32_t* block_tables;
+  int64_t table_row_stride;
+  const int64_t* sampled;
+  int32_t bs, block_size, n_patch;
+  int32_t patch_row[kMaxPatches], patch_col[kMaxPatches], patch_val[kMaxPatches];
+};
+
+__global__ void __launch_bounds__(128) advance_decode_state_kernel(const AdvanceParams p) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.bs) return;
+  int32_t* row = p.block_tables + static_cast<int64_t>(b) * p.table_row_stride;
+  // a row's new block id is written by the row's own thread, so no ordering between threads is needed
+#pragma unroll 1
+  for (int i = 0; i < p.n_patch; ++i)
+    if (p.patch_row[i] == b) row[p.patch_col[i]] = p.patch_val[i];
+  const int32_t len = p.context_lens[b] + 1;
+  const int32_t last = len - 1;                 // index of the token being appended
+  const int32_t blk = row[last / p.block_size];
+  p.input_ids[b] = p.sampled[b];
+  p.positions[b] = static_cast<int64_t>(len);   // the reference feeds len(seq), model_runner.py:251
+  p.context_lens[b] = len;
+  p.slot_mapping[b] = blk * p.block_size + last % p.block_size;
+}
+
+}  // namespace
+}  // namespace nvllm
+
+extern "C" int32_t nvllm_advance_decode_state_max_patches(void) { return nvllm::kMaxPatches; }
+
+extern "C" int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions, int32_t* slot_mapping,
+                                          int32_t* context_lens, int32_t* block_tables, int64_t table_row_stride,
+                                          const int64_t* sampled_tokens, int32_t bs, int32_t block_size,
+                                          const int32_t* patch_rows, const int32_t* patch_cols,
+                                          const int32_t* patch_vals, int32_t n_patch, void* stream) {
+  using namespace nvllm;
+  if (bs == 0) return NVLLM_OK;
+  if (!input_ids || !positions || !slot_mapping || !context_lens || !block_tables || !sampled_tokens || bs < 0 ||
+      block_size <= 0 || table_row_stride <= 0 || n_patch < 0)
+    return NVLLM_ERR_BAD_ARG;
+  if (n_patch > kMaxPatches) return NVLLM_ERR_UNSUPPORTED;
+  if (n_patch > 0 && (!patch_rows || !patch_cols || !patch_vals)) return NVLLM_ERR_BAD_ARG;
+  AdvanceParams p = {};
+  p.input_ids = input_ids;
+  p.positions = positions;
+  p.slot_mapping = slot_mapping;
+  p.context_lens = context_lens;
+  p.block_tables = block_tables;
+  p.table_row_stride = table_row_stride;
+  p.sampled = sampled_tokens;
+  p.bs = bs;
+  p.block_size = block_size;
+  p.n_patch = n_patch;
+  for (int i = 0; i < n_patch; ++i) {
+    if (patch_rows[i] < 0 || patch_rows[i] >= bs || patch_cols[i] < 0 || patch_cols[i] >= table_row_stride) return NVLLM_ERR_BAD_ARG;
+    p.patch_row[i] = patch_rows[i];
+    p.patch_col[i] = patch_cols[i];
+    p.patch_val[i] = patch_vals[i];
+  }
+  advance_decode_state_kernel<<<(bs + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  note_launch();
+  return record_cuda_error(cudaGetLastError());
+}

@@ -93,6 +93,7 @@ struct SampleParams {
   const float* noise;        // optional [bs, vocab] fp32 exponential samples
   int64_t noise_row_stride;
   int64_t* tokens;
+  int64_t* tokens_host;      // optional second copy (mapped pinned host memory), vocabulary-parallel mode
   int* counters;
   float4* partials;          // [bs][chunks] = (greedy value, greedy index, sample key, sample index)
   int vocab, chunk_elems, chunks;
@@ -399,6 +400,7 @@ __global__ void __launch_bounds__(kSampleThreads, 4) sample_tokens_kernel(const 
     int tok = f.i;
     if (tok == INT_MAX) tok = 0;   // a row whose every key is -inf: torch.argmax answers 0
     p.tokens[row] = static_cast<int64_t>(tok);
+    if (p.tokens_host) p.tokens_host[row] = static_cast<int64_t>(tok);
     if (p.world > 1) {
       // the call is complete on this rank once every row has swapped: the last row advances the call epoch
       XchgControl* ctl = reinterpret_cast<XchgControl*>(p.comm[p.rank]);
@@ -444,7 +446,7 @@ uint32_t* sampler_host_error_word() {
   return word;
 }
 
-int launch_sampler(int64_t* tokens_out, const void* logits, int32_t logits_elem_bytes, int64_t logits_row_stride,
+int launch_sampler(int64_t* tokens_out, int64_t* tokens_host, const void* logits, int32_t logits_elem_bytes, int64_t logits_row_stride,
                    const float* temperatures, const float* noise, int64_t noise_row_stride, int32_t bs, int32_t vocab,
                    int32_t vocab_offset, uint64_t seed, uint64_t offset, void* workspace, size_t workspace_bytes,
                    void* const* comm_ptrs, size_t comm_bytes, int32_t rank, int32_t world, void* stream) {
@@ -499,6 +501,7 @@ int launch_sampler(int64_t* tokens_out, const void* logits, int32_t logits_elem_
   p.noise = noise;
   p.noise_row_stride = noise_row_stride;
   p.tokens = tokens_out;
+  p.tokens_host = tokens_host;
   p.counters = static_cast<int*>(workspace);
   p.partials = reinterpret_cast<float4*>(static_cast<char*>(workspace) + kCounterBytes);
   p.vocab = vocab;
@@ -530,7 +533,7 @@ extern "C" int nvllm_sample_tokens(int64_t* tokens_out, const void* logits, int3
                                    int64_t logits_row_stride, const float* temperatures, const float* noise,
                                    int64_t noise_row_stride, int32_t bs, int32_t vocab, uint64_t seed,
                                    uint64_t offset, void* workspace, size_t workspace_bytes, void* stream) {
-  return nvllm::launch_sampler(tokens_out, logits, logits_elem_bytes, logits_row_stride, temperatures, noise,
+  return nvllm::launch_sampler(tokens_out, nullptr, logits, logits_elem_bytes, logits_row_stride, temperatures, noise,
                                noise_row_stride, bs, vocab, 0, seed, offset, workspace, workspace_bytes, nullptr, 0, 0, 1,
                                stream);
 }
@@ -541,14 +544,15 @@ extern "C" size_t nvllm_sample_comm_bytes(int32_t world, int32_t max_bs) {
   return need < nvllm::kXchgMinBytes ? nvllm::kXchgMinBytes : need;
 }
 
-extern "C" int nvllm_sample_tokens_sharded(int64_t* tokens_out, const void* logits_shard, int32_t logits_elem_bytes,
+extern "C" int nvllm_sample_tokens_sharded(int64_t* tokens_out, int64_t* tokens_out_host, const void* logits_shard,
+                                           int32_t logits_elem_bytes,
                                            int64_t logits_row_stride, const float* temperatures,
                                            const float* noise_shard, int64_t noise_row_stride, int32_t bs,
                                            int32_t vocab_shard, int32_t vocab_offset, uint64_t seed, uint64_t offset,
                                            void* workspace, size_t workspace_bytes, void* const* comm_ptrs,
                                            size_t comm_bytes, int32_t rank, int32_t world, void* stream) {
   if (world < 2) return NVLLM_ERR_BAD_ARG;
-  return nvllm::launch_sampler(tokens_out, logits_shard, logits_elem_bytes, logits_row_stride, temperatures, noise_shard,
+  return nvllm::launch_sampler(tokens_out, tokens_out_host, logits_shard, logits_elem_bytes, logits_row_stride, temperatures, noise_shard,
                                noise_row_stride, bs, vocab_shard, vocab_offset, seed, offset, workspace, workspace_bytes,
                                comm_ptrs, comm_bytes, rank, world, stream);
 }

@@ -296,12 +296,14 @@ def _sample_workspace(device: torch.device, bs: int, key) -> torch.Tensor:
 
 def sample_tokens_sharded(logits_shard: torch.Tensor, temperatures: Optional[torch.Tensor], vocab_offset: int, comm,
                           noise: Optional[torch.Tensor] = None, seed: int = 0, offset: int = 0,
-                          out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                          out: Optional[torch.Tensor] = None, host_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Vocabulary-parallel Sampler: replaces the logits gather of ParallelLMHead.forward
     (nanovllm/layers/embed_head.py:66-70) + Sampler.forward on rank 0 (nanovllm/layers/sampler.py:10-18).
     `logits_shard` [bs, vocab/tp] are this rank's columns [vocab_offset, vocab_offset + vocab/tp) of the full logits;
     `comm` is a TPComm sized with sampler_cuda.comm_bytes().  Every rank gets the int64 token ids [bs], equal to
-    sample_tokens() on the concatenated logits.  `out` may be a pinned host tensor (written through its mapping).
+    sample_tokens() on the concatenated logits.  `host_out` (pinned int64 host tensor) receives a second copy of the
+    ids, written by the kernel through the buffer's device mapping: the host reads them after a stream/event
+    synchronise with no device-to-host copy (what `.tolist()` does at engine/model_runner.py:311).
     `temperatures` may be None on ranks > 0: rank 0's are used (it hands them over inside the kernel)."""
     lib = _lib.load()
     _require_cuda(logits_shard, temperatures, noise)
@@ -318,12 +320,15 @@ def sample_tokens_sharded(logits_shard: torch.Tensor, temperatures: Optional[tor
         out = torch.empty(bs, dtype=torch.int64, device=logits_shard.device)
     else:
         assert out.dtype == torch.int64 and out.numel() >= bs and out.is_contiguous() and (out.is_cuda or out.is_pinned())
+    if host_out is not None:
+        assert host_out.dtype == torch.int64 and host_out.numel() >= bs and host_out.is_contiguous() and host_out.is_pinned()
     if bs == 0:
         return out
     idx = logits_shard.device.index if logits_shard.device.index is not None else torch.cuda.current_device()
     # one workspace per (device, communicator): ranks sharing a device (loop-back tests) launch concurrently
     ws = _sample_workspace(logits_shard.device, bs, (idx, comm.local_ptr))
-    st = lib.nvllm_sample_tokens_sharded(out.data_ptr(), logits_shard.data_ptr(), logits_shard.element_size(),
+    st = lib.nvllm_sample_tokens_sharded(out.data_ptr(), host_out.data_ptr() if host_out is not None else None,
+                                         logits_shard.data_ptr(), logits_shard.element_size(),
                                          logits_shard.stride(0),
                                          temperatures.data_ptr() if temperatures is not None else None,
                                          noise.data_ptr() if noise is not None else None,

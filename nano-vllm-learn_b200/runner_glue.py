@@ -11,7 +11,13 @@ B200-first differences (host side only, results unchanged):
     rows, -1-padded table columns inside the live width, exactly what `zero_()` + row copies
     produce in the reference), so replay needs no extra device ops;
   * a small ring of staging slots guarded by CUDA events keeps worker ranks (which never sync with
-    the host) from overwriting a slot whose copy is still in flight.
+    the host) from overwriting a slot whose copy is still in flight;
+  * device-side decode state: while the running batch is unchanged from one decode
+    step to the next, nothing is staged on the host at all -- one tiny kernel (nvllm_advance_decode_state)
+    takes input_ids from the sampler's device output, bumps positions / context_lens, recomputes the slots
+    from the table already on the device and patches in the few block ids BlockManager.may_append opened
+    for this step (passed as kernel arguments).  Any change of batch composition, layout or an intervening
+    prefill falls back to the staged path, which re-publishes everything.
 The engine-facing quirks are kept on purpose: decode `positions = len(seq)` (model_runner.py:251),
 zero padding of graph rows (:291-293), `block_tables` only when a prefix hit exists (:225-232).
 """
@@ -86,6 +92,15 @@ class RunnerGlue:
         self._host_view_cache: dict = {}
         self._dev_view_cache: dict = {}
         self.graph_bs: Optional[list[int]] = None   # set by capture; enables the bucketed decode layout
+        # device-side decode state: what the device buffers hold after the last decode step (None = unknown)
+        import os
+        self.device_state = self.pinned and os.environ.get("NVLLM_DEVICE_DECODE_STATE", "1") != "0"
+        self._fast = None
+        self._max_patches = int(self.lib.nvllm_advance_decode_state_max_patches())
+        self._patch = np.zeros((3, self._max_patches), dtype=np.int32)
+        self._patch_ptrs = tuple(_i32ptr(self._patch[i]) for i in range(3))
+        self.fast_steps = 0      # decode steps served by the device-side path (tests, profiling)
+        self.staged_steps = 0
 
     # ------------------------------------------------------------------ layouts
     @staticmethod
@@ -130,6 +145,7 @@ class RunnerGlue:
         width = max(len(s.block_table) for s in seqs)
         n = len(seqs)
         self._slot_sig = [None] * self.RING
+        self._fast = None
         slot = self._next_slot()
         tab = slot.np[:4 * n * width].view(np.int32).reshape(n, width)
         tab.fill(-1)
@@ -160,6 +176,7 @@ class RunnerGlue:
         if end > self.dev.numel():
             raise ValueError("prefill batch exceeds max_num_batched_tokens/max_num_seqs staging capacity")
         self._slot_sig = [None] * self.RING   # new sequences may reuse freed blocks: no decode table survives a prefill
+        self._fast = None                     # and the prefill staging overwrites the device buffer
         slot = self._next_slot()
         h = slot.np
         ids = h[o_ids:o_ids + 8 * total_q].view(np.int64)
@@ -243,9 +260,63 @@ class RunnerGlue:
             self._dev_view_cache[key] = v
         return v
 
-    def prepare_decode(self, seqs: Sequence):
+    def _advance_on_device(self, seqs: Sequence, ids_key: tuple, device_tokens: torch.Tensor):
+        """One decode step of an unchanged batch without host staging; None -> the caller takes the staged path."""
+        st = self._fast
+        if st is None or st["ids"] != ids_key or device_tokens is None:
+            return None
+        bs, bsz = st["bs"], self.block_size
+        lens = st["lens"]
+        lens += 1
+        if len(seqs[0]) != lens[0] or len(seqs[-1]) != lens[-1]:      # not "one more token each": restage
+            self._fast = None
+            return None
+        opened = np.flatnonzero((lens - 1) % bsz == 0)                 # rows whose new token starts a block
+        n_patch = int(opened.size)
+        width = st["width"]
+        if n_patch:
+            if n_patch > self._max_patches:
+                self._fast = None
+                return None
+            cols = (lens[opened] - 1) // bsz
+            new_width = max(width, int(cols.max()) + 1)
+            if new_width != width and st["gbs"] is None:               # eager layout is [bs, width]: it changes
+                self._fast = None
+                return None
+            width = st["width"] = new_width
+            self._patch[0, :n_patch] = opened
+            self._patch[1, :n_patch] = cols
+            self._patch[2, :n_patch] = [seqs[i].block_table[-1] for i in opened]
+        rows, cols_l = st["rows"], st["cols"]
+        d_ids, d_pos, d_slots, d_lens, d_tab, _, _ = self._dev_decode_views(rows, cols_l, bs, width)
+        ptrs = st.get("ptrs")
+        if ptrs is None:
+            f_ids, f_pos, f_slots, f_lens, f_tab = self.decode_views(self.dev, rows, cols_l)
+            ptrs = st["ptrs"] = (f_ids.data_ptr(), f_pos.data_ptr(), f_slots.data_ptr(), f_lens.data_ptr(),
+                                 f_tab.data_ptr(), cols_l)
+        rc = self.lib.nvllm_advance_decode_state(ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], ptrs[5],
+                                                 device_tokens.data_ptr(), bs, bsz, *self._patch_ptrs, n_patch,
+                                                 torch.cuda.current_stream().cuda_stream)
+        if rc != 0:
+            self._fast = None
+            _lib.check(rc, "advance_decode_state")
+        self.fast_steps += 1
+        self.set_context(False, slot_mapping=d_slots, context_lens=d_lens, block_tables=d_tab)
+        return d_ids, d_pos
+
+    def prepare_decode(self, seqs: Sequence, device_tokens: Optional[torch.Tensor] = None):
+        """`device_tokens`: the sampler's int64 output of the PREVIOUS step, still on the device, row i = seqs[i]
+        (sampler_cuda.Sampler.last_tokens); enables the device-side path for an unchanged batch."""
         bsz = self.block_size
         bs = len(seqs)
+        ids_key = None
+        if self.device_state:
+            ids_key = tuple([s.seq_id for s in seqs]) if hasattr(seqs[0], "seq_id") else None
+            if ids_key is not None and device_tokens is not None and self._fast is not None:
+                out = self._advance_on_device(seqs, ids_key, device_tokens)
+                if out is not None:
+                    return out
+        self.staged_steps += 1
         tables = [s.block_table for s in seqs]
         width = max(map(len, tables))
         gbs = self.decode_bucket(bs)
@@ -292,6 +363,9 @@ class RunnerGlue:
         d_ids, d_pos, d_slots, d_lens, d_tab, d_all, h_all = self._dev_decode_views(rows, cols, bs, width)
         d_all.copy_(h_all[slot_idx], non_blocking=True)
         slot.mark()
+        if ids_key is not None:
+            self._fast = dict(ids=ids_key, rows=rows, cols=cols, bs=bs, width=width, gbs=gbs,
+                              lens=np.asarray(n_tok, dtype=np.int64))
         self.set_context(False, slot_mapping=d_slots, context_lens=d_lens, block_tables=d_tab)
         return d_ids, d_pos
 
@@ -332,7 +406,11 @@ def install(model_runner_cls, set_context: Callable, get_context: Callable, rese
         return _glue(self).prepare_prefill(seqs) if _is_cuda(self) else orig["prepare_prefill"](self, seqs)
 
     def prepare_decode(self, seqs):
-        return _glue(self).prepare_decode(seqs) if _is_cuda(self) else orig["prepare_decode"](self, seqs)
+        if not _is_cuda(self):
+            return orig["prepare_decode"](self, seqs)
+        # the fused sampler keeps its output on the device (sampler_cuda.Sampler.last_tokens): an unchanged batch is
+        # advanced there instead of being re-staged from the host
+        return _glue(self).prepare_decode(seqs, getattr(self.sampler, "last_tokens", None))
 
     @torch.inference_mode()
     def run_model(self, input_ids, positions, is_prefill):

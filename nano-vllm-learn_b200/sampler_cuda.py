@@ -47,11 +47,22 @@ class Sampler(nn.Module):
         self._calls = 0
         self._comm: TPComm | None = None
         self._host_tokens: torch.Tensor | None = None
+        self._dev_tokens: torch.Tensor | None = None
+        # int64 ids of the most recent call, still on the device: the runner glue feeds them to the next decode step
+        # as input_ids without a host round trip (runner_glue.RunnerGlue.prepare_decode)
+        self.last_tokens: torch.Tensor | None = None
+
+    def _out(self, bs: int, device) -> torch.Tensor:
+        if self._dev_tokens is None or self._dev_tokens.numel() < bs or self._dev_tokens.device != device:
+            self._dev_tokens = torch.empty(max(bs, MAX_BS), dtype=torch.int64, device=device)
+        return self._dev_tokens[:bs]
 
     @torch.inference_mode()
     def forward(self, logits: torch.Tensor, temperatures: torch.Tensor, noise: torch.Tensor | None = None):
         self._calls += 1
-        return ops.sample_tokens(logits, temperatures, noise=noise, seed=torch.initial_seed(), offset=self._calls)
+        self.last_tokens = ops.sample_tokens(logits, temperatures, noise=noise, seed=torch.initial_seed(),
+                                             offset=self._calls, out=self._out(logits.shape[0], logits.device))
+        return self.last_tokens
 
     # ---- vocabulary-parallel mode ---------------------------------------------------------------------------------
     def bind_comm(self, comm: TPComm) -> None:
@@ -74,14 +85,17 @@ class Sampler(nn.Module):
         comm = self._get_comm()
         self._calls += 1
         bs, shard = logits_shard.shape
-        out = None
+        host = None
         if to_host:
             if self._host_tokens is None or self._host_tokens.numel() < bs:
                 self._host_tokens = torch.empty(max(bs, MAX_BS), dtype=torch.int64, device="cpu", pin_memory=True)
-            out = self._host_tokens
+            host = self._host_tokens
         tokens = ops.sample_tokens_sharded(logits_shard, temperatures, comm.rank * shard, comm, noise=noise_shard,
-                                           seed=torch.initial_seed(), offset=self._calls, out=out)
+                                           seed=torch.initial_seed(), offset=self._calls,
+                                           out=self._out(bs, logits_shard.device), host_out=host)
+        self.last_tokens = tokens
         if to_host:
+            tokens = host
             torch.cuda.current_stream().synchronize()
             err = poll_error()
             if err:

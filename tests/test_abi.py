@@ -171,7 +171,7 @@ def test_sharded_sampler_host_arithmetic_without_gpu(lib):
 
     def call(**kw):
         a = dict(base, **kw)
-        return lib.nvllm_sample_tokens_sharded(a["out"], a["logits"], a["eb"], a["stride"], a["temps"], a["noise"], a["ns"],
+        return lib.nvllm_sample_tokens_sharded(a["out"], None, a["logits"], a["eb"], a["stride"], a["temps"], a["noise"], a["ns"],
                                                a["bs"], a["vocab"], a["off"], 0, 0, a["ws"], a["wsb"], a["comm"], a["cb"],
                                                a["rank"], a["world"], None)
     assert call(world=1) == 1
