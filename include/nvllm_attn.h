@@ -305,6 +305,9 @@ NVLLM_API int64_t nvllm_prepare_prefill_slots(const int32_t* block_table,
  *   patch_* are HOST arrays of n_patch <= nvllm_advance_decode_state_max_patches()
  *   entries (the blocks may_append opened for this step), passed to the kernel
  *   by value: no host-to-device copy.  Everything else is device memory.
+ *   Columns [pad_col_begin, pad_col_end) of every row are set to -1 first:
+ *   when a new block widens the live table, the other rows carry the
+ *   reference's -1 padding there (prepare_block_tables, :163-166).
  * ---------------------------------------------------------------------- */
 NVLLM_API int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions,
                                int32_t* slot_mapping, int32_t* context_lens,
@@ -312,7 +315,8 @@ NVLLM_API int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions,
                                const int64_t* sampled_tokens, int32_t bs,
                                int32_t block_size, const int32_t* patch_rows,
                                const int32_t* patch_cols, const int32_t* patch_vals,
-                               int32_t n_patch, void* stream);
+                               int32_t n_patch, int32_t pad_col_begin,
+                               int32_t pad_col_end, void* stream);
 NVLLM_API int32_t nvllm_advance_decode_state_max_patches(void);
 
 /* ------------------------------------------------------------------------

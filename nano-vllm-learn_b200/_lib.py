@@ -65,7 +65,7 @@ SIGNATURES = {
     "nvllm_rowparallel_plan": (c_int, [c_int32, c_int32, c_int32, c_int32, _P32, _P32, _P32]),
     "nvllm_rowparallel_set_plan": (c_int, [c_int32, c_int32, c_int32, c_int64]),
     "nvllm_advance_decode_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int32,
-                                           c_int32, _P32, _P32, _P32, c_int32, c_void_p]),
+                                           c_int32, _P32, _P32, _P32, c_int32, c_int32, c_int32, c_void_p]),
     "nvllm_advance_decode_state_max_patches": (c_int32, []),
     "nvllm_prepare_decode_slots": (c_int, [_P32, _P32, c_int32, c_int32, _P32]),
     "nvllm_prepare_prefill_slots": (c_int64, [_P32, c_int32, c_int32, c_int32, c_int32, _P32, c_int64]),

@@ -29,6 +29,7 @@ struct AdvanceParams {
   int64_t table_row_stride;
   const int64_t* sampled;
   int32_t bs, block_size, n_patch;
+  int32_t pad_col_begin, pad_col_end;   // table columns that join the live width this step: -1 like the reference's padding
   int32_t patch_row[kMaxPatches], patch_col[kMaxPatches], patch_val[kMaxPatches];
 };
 
@@ -37,6 +38,7 @@ __global__ void __launch_bounds__(128) advance_decode_state_kernel(const Advance
   if (b >= p.bs) return;
   int32_t* row = p.block_tables + static_cast<int64_t>(b) * p.table_row_stride;
   // a row's new block id is written by the row's own thread, so no ordering between threads is needed
+  for (int c = p.pad_col_begin; c < p.pad_col_end; ++c) row[c] = -1;
 #pragma unroll 1
   for (int i = 0; i < p.n_patch; ++i)
     if (p.patch_row[i] == b) row[p.patch_col[i]] = p.patch_val[i];
@@ -58,13 +60,16 @@ extern "C" int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions
                                           int32_t* context_lens, int32_t* block_tables, int64_t table_row_stride,
                                           const int64_t* sampled_tokens, int32_t bs, int32_t block_size,
                                           const int32_t* patch_rows, const int32_t* patch_cols,
-                                          const int32_t* patch_vals, int32_t n_patch, void* stream) {
+                                          const int32_t* patch_vals, int32_t n_patch, int32_t pad_col_begin,
+                                          int32_t pad_col_end, void* stream) {
   using namespace nvllm;
   if (bs == 0) return NVLLM_OK;
   if (!input_ids || !positions || !slot_mapping || !context_lens || !block_tables || !sampled_tokens || bs < 0 ||
       block_size <= 0 || table_row_stride <= 0 || n_patch < 0)
     return NVLLM_ERR_BAD_ARG;
   if (n_patch > kMaxPatches) return NVLLM_ERR_UNSUPPORTED;
+  if (pad_col_begin < 0 || pad_col_end > table_row_stride || (pad_col_end > pad_col_begin && pad_col_end - pad_col_begin > 64))
+    return NVLLM_ERR_BAD_ARG;
   if (n_patch > 0 && (!patch_rows || !patch_cols || !patch_vals)) return NVLLM_ERR_BAD_ARG;
   AdvanceParams p = {};
   p.input_ids = input_ids;
@@ -77,6 +82,8 @@ extern "C" int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions
   p.bs = bs;
   p.block_size = block_size;
   p.n_patch = n_patch;
+  p.pad_col_begin = pad_col_begin;
+  p.pad_col_end = pad_col_end;
   for (int i = 0; i < n_patch; ++i) {
     if (patch_rows[i] < 0 || patch_rows[i] >= bs || patch_cols[i] < 0 || patch_cols[i] >= table_row_stride) return NVLLM_ERR_BAD_ARG;
     p.patch_row[i] = patch_rows[i];

@@ -273,7 +273,7 @@ class RunnerGlue:
             return None
         opened = np.flatnonzero((lens - 1) % bsz == 0)                 # rows whose new token starts a block
         n_patch = int(opened.size)
-        width = st["width"]
+        width = old_width = st["width"]
         if n_patch:
             if n_patch > self._max_patches:
                 self._fast = None
@@ -296,7 +296,7 @@ class RunnerGlue:
                                  f_tab.data_ptr(), cols_l)
         rc = self.lib.nvllm_advance_decode_state(ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], ptrs[5],
                                                  device_tokens.data_ptr(), bs, bsz, *self._patch_ptrs, n_patch,
-                                                 torch.cuda.current_stream().cuda_stream)
+                                                 old_width, width, torch.cuda.current_stream().cuda_stream)
         if rc != 0:
             self._fast = None
             _lib.check(rc, "advance_decode_state")

@@ -139,15 +139,30 @@ def test_batch_change_prefill_and_missing_tokens_fall_back(lib):
     _check(ctx, ids, pos, gorc.prepare_decode_ref(seqs), 6)
 
 
-def test_live_reference_trace_on_device(lib):
-    """The REAL BlockManager / Sequence / ModelRunner.prepare_decode (unmodified), 520 decode steps, every step."""
+@pytest.fixture
+def unmodified_reference():
+    """The UNMODIFIED reference package, imported for this test only: later tests import the edited integration copy
+    under the same package name (tests/test_gpu_engine_e2e.py), so every trace of it is removed again."""
+    import sys
     root = gorc.find_reference_root()
     if root is None:
         pytest.skip("reference not present")
+    before = set(sys.modules)
+    path_before = list(sys.path)
     try:
-        ref = gorc.ReferenceGlue(root)
-    except Exception as e:
-        pytest.skip(f"reference not importable: {e}")
+        try:
+            yield gorc.ReferenceGlue(root)
+        except ImportError as e:
+            pytest.skip(f"reference not importable: {e}")
+    finally:
+        for name in [m for m in sys.modules if m not in before and (m == "nanovllm" or m.startswith("nanovllm."))]:
+            del sys.modules[name]
+        sys.path[:] = path_before
+
+
+def test_live_reference_trace_on_device(lib, unmodified_reference):
+    """The REAL BlockManager / Sequence / ModelRunner.prepare_decode (unmodified), 520 decode steps, every step."""
+    ref = unmodified_reference
     import random
     random.seed(7)
     bm = ref.block_manager.BlockManager(128, BS)

@@ -1,5 +1,2 @@
-timeout 120 python -m pytest tests/test_gpu_prefill_tcgen05.py tests/test_gpu_parity.py -m gpu -x -q -k "prefill or prefix" > gpurun_out/r02_gpu_tests_o.log 2>&1; rc=$?; echo "tests rc=$rc"
-tail -3 gpurun_out/r02_gpu_tests_o.log
-if [ $rc -ne 0 ]; then exit 0; fi
-timeout 200 python tools/sweep_prefill.py --impls tcgen05 --flash > gpurun_out/r02_prefill_sweep_c.jsonl 2>&1; echo "sweep rc=$?"
-cut -c1-200 gpurun_out/r02_prefill_sweep_c.jsonl
+timeout 300 python -m pytest tests/test_gpu_decode_state.py tests/test_gpu_engine_e2e.py tests/test_gpu_sampler_sharded.py tests/test_gpu_sampler.py tests/test_gpu_multi_device.py -m gpu -x -q --timeout 200 > gpurun_out/r02_decode_state_tests.log 2>&1; echo "tests rc=$?"
+tail -5 gpurun_out/r02_decode_state_tests.log | cut -c1-300

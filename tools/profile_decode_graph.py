@@ -29,13 +29,14 @@ def main():
     seed(0)
     llm.generate(["warmup"], SamplingParams(max_tokens=1))
     prompts = [[randint(0, 10000) for _ in range(plen)] for _ in range(bs)]
-    for p, sp in zip(prompts, [SamplingParams(temperature=0.0, ignore_eos=True, max_tokens=64) for _ in range(bs)]):
+    for p, sp in zip(prompts, [SamplingParams(temperature=0.0, ignore_eos=True, max_tokens=128) for _ in range(bs)]):
         llm.add_request(p, sp)
     for _ in range(12):          # prefill + a few decode steps outside the profile
         llm.step()
     torch.cuda.synchronize()
+    N = 40
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
-        for _ in range(8):
+        for _ in range(N):
             llm.step()
         torch.cuda.synchronize()
     evs = sorted((e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA),
@@ -48,10 +49,27 @@ def main():
         agg[e.name[:90]][1] += d
         busy += d
     span = evs[-1].time_range.end - evs[0].time_range.start
-    print(f"backend={backend} bs={bs} prompt={plen}: 8 decode steps, span {span/8:.1f} us/step, "
-          f"kernel-busy {busy/8:.1f} us/step, {len(evs)/8:.0f} kernels/step")
+    # the host's share of the idle time: from the end of a step's last kernel (the sampler; any D2H copy of the ids
+    # follows it) to the first kernel of the next step's graph -- scheduler, glue, launch.  The rest of the idle time
+    # are the gaps between the ~260 small kernels INSIDE the captured graph, which no host code can shorten.
+    gaps = []
+    for i, e in enumerate(evs[:-1]):
+        if "sample_tokens_kernel" in e.name or "ArgMaxOps" in e.name:
+            nxt = next((x for x in evs[i + 1:] if not x.name.startswith("Memcpy") and not x.name.startswith("Memset")
+                        and "sample_tokens" not in x.name and "ArgMaxOps" not in x.name and "where" not in x.name), None)
+            if nxt is not None:
+                gaps.append(nxt.time_range.start - e.time_range.end)
+    if gaps:
+        gaps.sort()
+        print(f"between-step gap (sampler end -> next step's first kernel): median {gaps[len(gaps) // 2]:.1f} us, "
+              f"mean {sum(gaps) / len(gaps):.1f} us over {len(gaps)} steps")
+    glue = getattr(llm.model_runner, "_nvllm_glue", None)
+    print(f"backend={backend} bs={bs} prompt={plen}: {N} decode steps, span {span/N:.1f} us/step, "
+          f"kernel-busy {busy/N:.1f} us/step, {len(evs)/N:.0f} kernels/step, "
+          f"idle {100 * (span - busy) / span:.1f} % of the step; glue decode steps on device / staged: "
+          f"{getattr(glue, 'fast_steps', None)} / {getattr(glue, 'staged_steps', None)}")
     for name, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:22]:
-        print(f"{t/8:9.1f} us/step  n/step={n/8:6.1f}  avg={t/n:7.2f} us  {name}")
+        print(f"{t/N:9.1f} us/step  n/step={n/N:6.1f}  avg={t/n:7.2f} us  {name}")
     llm.exit()
 
 
