@@ -358,6 +358,13 @@ def run_cuda(args):
         except Exception as e:
             vp_sampler = {"failed": f"{type(e).__name__}: {e}"[:300]}
 
+    fused_emb = None
+    if dist is not None and not args.no_fused_allreduce:
+        try:
+            fused_emb = run_fused_embedding(args, dev, rank, world, ops, dist)
+        except Exception as e:
+            fused_emb = {"failed": f"{type(e).__name__}: {e}"[:300]}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, sample_bs=args.cpu_sample_bs, iters=None)
@@ -392,7 +399,7 @@ def run_cuda(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
             "cpu_baseline": cpu, "vs_flash": vs_flash, "tp_strong": tp_strong, "long_ctx": long_ctx,
             "prefill": prefill, "fused_allreduce": fused, "vocab_parallel_sampler": vp_sampler,
-            "tp_e2e": tp_e2e}
+            "fused_embedding": fused_emb, "tp_e2e": tp_e2e}
     print(json.dumps(line), flush=True)
 
 
@@ -578,13 +585,16 @@ def run_long_ctx(args, dev, ops):
     peak, _ = peaks()
     flash = None if args.no_flash else _flash_decode()
     rows = []
-    for bs, hq, hkv, tp in ((1, 32, 8, 1), (2, 32, 8, 1), (4, 32, 8, 1), (1, 4, 1, 8), (4, 4, 1, 8)):
-        r = _time_decode_shape(dev, ops, bs, 32768, hq, hkv, 160, seed=500 + bs + tp, flash=flash)
+    # last row: BASELINE configs[0] (the reference's CPU-runnable case, bs=1 ctx=512 16q/8kv, 2 pages) on the GPU, so
+    # the CPU milliseconds of BASELINE.md §2 have a GPU figure beside them (launch-latency bound: 2.1 MB of traffic)
+    for bs, hq, hkv, tp, ctx, width in ((1, 32, 8, 1, 32768, 160), (2, 32, 8, 1, 32768, 160), (4, 32, 8, 1, 32768, 160),
+                                        (1, 4, 1, 8, 32768, 160), (4, 4, 1, 8, 32768, 160), (1, 16, 8, 1, 512, 2)):
+        r = _time_decode_shape(dev, ops, bs, ctx, hq, hkv, width, seed=500 + bs + tp, flash=flash)
         us = r["us"]["median"]
         gus = r["graph_us_per_launch"]
         # headline of the row = the in-graph per-launch time (decode runs inside CUDA graphs in the engine, and a 12-30 us
         # launch issued from Python is host-bound); the stream-issued figure is kept beside it
-        row = {"bs": bs, "ctx": 32768, "heads": f"{hq}q/{hkv}kv (tp={tp} shard)", "graph_us_per_launch": gus,
+        row = {"bs": bs, "ctx": ctx, "heads": f"{hq}q/{hkv}kv (tp={tp} shard)", "graph_us_per_launch": gus,
                "GBps": round(r["algorithmic_bytes"] / gus / 1e3, 1),
                "frac_of_measured_peak": round(r["algorithmic_bytes"] / gus / 1e3 / peak, 4),
                "stream_us": us, "stream_us_min": r["us"]["min"], "stream_us_max": r["us"]["max"],
@@ -593,6 +603,8 @@ def run_long_ctx(args, dev, ops):
         if isinstance(r.get("flash_us"), dict):
             row["flash_attn_us"] = r["flash_us"]["median"]
             row["flash_attn_graph_us_per_launch"] = r.get("flash_graph_us_per_launch")
+        if r["algorithmic_bytes"] * r["input_copies_rotated"] < (126 << 20):
+            row["l2"] = "all rotated copies together fit the 126 MB L2: a latency figure, not an HBM one"
         rows.append(row)
     return rows
 
@@ -780,6 +792,81 @@ def run_fused_allreduce(args, dev, rank, world, ops, dist):
     dist.barrier()
     rp.release() if False else None
     return {"parity_ok": all_ok, "world": world, "transport": comm.how, "timeout_latch": rp.poll_error(),
+            "timing": f"CUDA-graph chains of {chain} calls x {iters} replays, max over ranks", "rows": rows}
+
+
+def run_fused_embedding(args, dev, rank, world, ops, dist):
+    """SURVEY §8f rank 2, third collective, N > 1 only: the fused VocabParallelEmbedding (lookup + row exchange in one
+    launch over NVLink peer memory) beside the reference's masked F.embedding + dist.all_reduce
+    (nanovllm/layers/embed_head.py:35-43), Qwen3-0.6B (hidden 1024) and Qwen3-8B (hidden 4096) tables at
+    tensor_parallel_size = N.  Parity: bit-identical to the reference formula on every rank.  Then device time per call,
+    CUDA-graph chains, max over ranks."""
+    import torch.nn.functional as F
+    from nano_vllm_learn_b200 import embedding_cuda
+    from nano_vllm_learn_b200.rowparallel_cuda import TPComm
+    vocab = 151936
+    if vocab % world:
+        return {"skipped": f"vocab {vocab} not divisible by {world}"}
+    per = vocab // world
+    _lib = __import__("nano_vllm_learn_b200._lib", fromlist=["x"])
+    _lib.check(_lib.load().nvllm_vocab_embedding_set_timeout_ms(5000), "set_timeout")
+    rows, all_ok = [], True
+    chain, iters = 28, 5
+    for hidden in (1024, 4096):
+        comm = TPComm.from_process_group(embedding_cuda.comm_bytes(world, hidden))
+        gen = torch.Generator(device=dev).manual_seed(4000 + hidden + rank)
+        w = torch.empty(per, hidden, dtype=torch.bfloat16, device=dev).normal_(generator=gen)
+        start = rank * per
+
+        def reference(x):
+            mask = (x >= start) & (x < start + per)
+            y = mask.unsqueeze(1) * F.embedding(mask * (x - start), w)
+            dist.all_reduce(y)
+            return y
+
+        for n in (1, 16, 64, 256, 512):
+            gx = torch.Generator(device=dev).manual_seed(77 + n)            # same ids on every rank
+            x = torch.randint(0, vocab, (n,), generator=gx, device=dev)
+            y = ops.vocab_parallel_embedding(x, w, start, comm)
+            want = reference(x)
+            torch.cuda.synchronize()
+            flag = torch.tensor([1 if (torch.equal(y, want) and embedding_cuda.poll_error() == 0) else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok = bool(flag.item())
+            all_ok = all_ok and ok
+            row = {"hidden": hidden, "tokens": n, "parity_ok": ok, "nvlink_push_bytes_per_owner_row": hidden * 4 * (world - 1)}
+            if ok:
+                out = torch.empty(n, hidden, dtype=torch.bfloat16, device=dev)
+
+                def timed(fn):
+                    for _ in range(2):
+                        fn()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        for _ in range(chain):
+                            fn()
+                    g.replay()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(iters):
+                        g.replay()
+                    b.record()
+                    torch.cuda.synchronize()
+                    t = torch.tensor([a.elapsed_time(b) * 1e3 / (iters * chain)], dtype=torch.float64, device=dev)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    del g
+                    return round(float(t.item()), 2)
+                row["us_fused"] = timed(lambda: ops.vocab_parallel_embedding(x, w, start, comm, out=out))
+                row["us_nccl"] = timed(lambda: reference(x))
+                row["speedup"] = round(row["us_nccl"] / row["us_fused"], 2)
+            rows.append(row)
+        torch.cuda.synchronize()
+        dist.barrier()
+    return {"parity_ok": all_ok, "world": world, "timeout_latch": embedding_cuda.poll_error(),
             "timing": f"CUDA-graph chains of {chain} calls x {iters} replays, max over ranks", "rows": rows}
 
 

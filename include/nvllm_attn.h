@@ -493,6 +493,41 @@ NVLLM_API int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit,
 /* Measurement and debug aids (read-bandwidth probe, prefill trace buffer) are not
  * part of this ABI: include/nvllm_tools.h, built into lib/libnvllm_tools.so. */
 
+/* ------------------------------------------------------------------------
+ * (7) fused VocabParallelEmbedding (the third collective
+ *     of a tensor-parallel step): embedding lookup + the exchange of the
+ *     looked-up rows in ONE launch per rank over NVLink peer memory.
+ *     reference: nanovllm/layers/embed_head.py:35-43 (VocabParallelEmbedding.
+ *                forward: masked F.embedding on the local vocabulary shard,
+ *                rows of foreign tokens zeroed, dist.all_reduce of [n, hidden])
+ *
+ *   y[t, :] = W[token_ids[t], :]  on every rank, where rank r holds rows
+ *   [vocab_start, vocab_start + vocab_per_rank) of W as `weight`
+ *   [vocab_per_rank, hidden] bf16.  The owner of a token writes the row to
+ *   its y and pushes it to every peer as 8-byte {bf16 x 2, call epoch} words;
+ *   the others poll their inbox.  Bit-exact copy of the owner's row (the
+ *   reference's sum adds world-1 zero rows to it).  n_tokens <= 512 (decode and
+ *   short prefill; longer batches keep the reference's NCCL path), hidden % 4
+ *   == 0, rows 8-byte aligned, 2 <= world <= 8.  Ids outside every shard are
+ *   outside the contract (the reference would produce a zero row).
+ *   Communicator: nvllm_vocab_embedding_comm_bytes(world, max_tokens, hidden)
+ *   bytes per rank from nvllm_tp_comm_alloc, mapped as in (6); every rank
+ *   passes the same max_tokens / hidden / comm_bytes.  Same calling rules as
+ *   (6): identical call sequence on all ranks, stream-ordered, graph-
+ *   capturable, no host synchronisation; timeout -> error latch
+ *   (nvllm_vocab_embedding_poll_error: 0 = none, else 1 + token row).
+ * ---------------------------------------------------------------------- */
+NVLLM_API size_t nvllm_vocab_embedding_comm_bytes(int32_t world, int32_t max_tokens, int32_t hidden);
+NVLLM_API int nvllm_vocab_parallel_embedding(void* y, int64_t y_row_stride,
+                                   const int64_t* token_ids, const void* weight,
+                                   int64_t w_row_stride, int32_t vocab_start,
+                                   int32_t vocab_per_rank, int32_t n_tokens,
+                                   int32_t hidden, int32_t max_tokens,
+                                   void* const* comm_ptrs, size_t comm_bytes,
+                                   int32_t rank, int32_t world, void* stream);
+NVLLM_API int nvllm_vocab_embedding_poll_error(uint32_t* error_out, int32_t clear);
+NVLLM_API int nvllm_vocab_embedding_set_timeout_ms(int64_t timeout_ms);
+
 #ifdef __cplusplus
 }
 #endif

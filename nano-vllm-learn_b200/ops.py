@@ -367,6 +367,34 @@ def rowparallel_linear_allreduce(x: torch.Tensor, weight: torch.Tensor, bias: Op
     return out
 
 
+EMBEDDING_MAX_TOKENS = 512
+
+
+def vocab_parallel_embedding(token_ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, comm,
+                             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused VocabParallelEmbedding.forward (nanovllm/layers/embed_head.py:35-43): lookup on this rank's vocabulary
+    shard `weight` [vocab/tp, hidden] bf16 (rows [vocab_start, vocab_start + vocab/tp) of the table) + the exchange of
+    the rows between ranks in one launch; `comm` is a TPComm sized with nvllm_vocab_embedding_comm_bytes(world,
+    EMBEDDING_MAX_TOKENS, hidden).  token_ids int64 [n], n <= 512.  Returns [n, hidden] bf16, identical on every rank."""
+    lib = _lib.load()
+    _require_cuda(token_ids, weight)
+    assert token_ids.dim() == 1 and token_ids.dtype == torch.int64 and token_ids.is_contiguous()
+    assert weight.dim() == 2 and weight.dtype == torch.bfloat16 and weight.stride(1) == 1
+    n = token_ids.numel()
+    vpr, hidden = weight.shape
+    if out is None:
+        out = torch.empty((n, hidden), dtype=torch.bfloat16, device=weight.device)
+    else:
+        assert out.shape == (n, hidden) and out.dtype == torch.bfloat16 and out.stride(1) == 1
+    if n == 0:
+        return out
+    st = lib.nvllm_vocab_parallel_embedding(out.data_ptr(), out.stride(0), token_ids.data_ptr(), weight.data_ptr(),
+                                            weight.stride(0), vocab_start, vpr, n, hidden, EMBEDDING_MAX_TOKENS,
+                                            comm.ptr_array, comm.nbytes, comm.rank, comm.world, _stream())
+    _lib.check(st, "vocab_parallel_embedding")
+    return out
+
+
 def rowparallel_plan(n_tokens: int, in_features_per_rank: int, out_features: int, world: int) -> tuple[int, int, int]:
     """(feature_tile, ksplit, mode) the library will use for this shape (needs a CUDA device)."""
     import ctypes

@@ -27,10 +27,14 @@ MAX_TOKENS = 512          # nvllm_rowparallel_linear_allreduce's n_tokens limit 
 _ENV_MAX = os.environ.get("NVLLM_FUSED_ALLREDUCE_MAX_TOKENS")
 
 
-def engine_max_tokens(in_features_per_rank: int, out_features: int) -> int:
+def engine_max_tokens(in_features_per_rank: int, out_features: int, world: int = 2) -> int:
     if _ENV_MAX is not None:
         return min(MAX_TOKENS, int(_ENV_MAX))
     wbytes = in_features_per_rank * out_features * 2
+    if world >= 4:
+        # round 2, 4 B200s (profiles/r02_bench_n4.json): every shard 1.1-1.5x at 64 tokens, 0.64-0.96x at 256 -- the
+        # one-shot exchange pushes world-1 fp32 copies, so the break-even moves down as the world grows
+        return 128 if wbytes <= (4 << 20) else 64
     return 256 if wbytes <= (4 << 20) else 64 if wbytes <= (16 << 20) else 32
 
 
@@ -166,10 +170,10 @@ _COMM: TPComm | None = None
 _SHAPES: set[tuple[int, int]] = set()
 _ENABLED = False
 # NVLLM_FUSED_ALLREDUCE: "1" fused kernel, "0" the reference's F.linear + NCCL all_reduce.  Unset: fused at the world
-# sizes where the FINAL kernel (flag-in-data exchange) passed tests/test_gpu_rowparallel.py and ran the engine end to end
-# on B200s -- 2 GPUs.  4 GPUs ran green and +19..30 % end to end with the previous exchange (v3) and 8 GPUs were not run:
-# both opt in with "1" until they are re-run.
-VALIDATED_WORLDS = (2,)
+# sizes where the FINAL kernel (flag-in-data exchange) passed tests/test_gpu_rowparallel*.py on B200s and bench.py's
+# fused_allreduce leg reported parity_ok: 2 GPUs (profiles/r02_tp2_tests.log, r02_bench_n2.json) and 4 GPUs
+# (profiles/r02_tp4_tests.log, r02_bench_n4.json).  Other world sizes opt in with "1".
+VALIDATED_WORLDS = (2, 4)
 
 
 def configure(cuda_backend: bool) -> None:
@@ -238,7 +242,7 @@ def install(RowParallelLinear) -> None:
                                  supported(self.input_size_per_partition, self.output_size, self.tp_size))
         if self._nvllm_fused:
             _SHAPES.add((self.input_size_per_partition, self.output_size))
-        self._nvllm_fused_max = engine_max_tokens(self.input_size_per_partition, self.output_size)
+        self._nvllm_fused_max = engine_max_tokens(self.input_size_per_partition, self.output_size, self.tp_size)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not getattr(self, "_nvllm_fused", False) or x.dim() != 2 or x.shape[0] > self._nvllm_fused_max or \

@@ -208,6 +208,28 @@ def make_lm_head_case(name: str):
                 cu_seqlens_q=None if cu is None else torch.tensor(cu, dtype=torch.int32), noise_seed=2000 + seed)
 
 
+# ---- fused VocabParallelEmbedding (third collective) ----------------------------------------
+# name -> (seed, n_tokens, vocab, hidden, world)
+EMBEDDING_CASES = {
+    "emb_tp2": (60, 16, 4096, 256, 2),
+    "emb_tp4_ragged": (61, 5, 2048, 128, 4),
+    "emb_tp8": (62, 33, 1024, 64, 8),
+    "emb_one_owner_tp2": (63, 8, 1024, 1024, 2),      # every token in rank 1's shard: rank 1 waits for nobody
+}
+
+
+def make_embedding_case(name: str):
+    seed, n, vocab, hidden, world = EMBEDDING_CASES[name]
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(vocab, hidden, generator=g).to(torch.bfloat16)
+    if name == "emb_one_owner_tp2":
+        x = torch.randint(vocab // 2, vocab, (n,), generator=g)
+    else:
+        x = torch.randint(0, vocab, (n,), generator=g)
+        x[0], x[-1] = 0, vocab - 1                     # shard edges
+    return dict(x=x.to(torch.int64), weight=w, world=world)
+
+
 # ---- fused RowParallelLinear -------------------------------------------------------------
 # name -> (seed, n_tokens, in_features (all ranks), out_features, world, bias)
 ROWPARALLEL_CASES = {

@@ -7,9 +7,10 @@ greedy requests once per arm, each arm in its own process:
     nccl      cuda backend, reference collectives: F.linear + dist.all_reduce, lm_head dist.gather + rank-0 sampler
     vp        + vocabulary-parallel sampling (edit A8) -- the model path is untouched, so the token ids must be
               IDENTICAL to `nccl` (logits are the same bits; only where the arg-max is taken changes)
+    emb       + fused VocabParallelEmbedding (edit A9) -- a bit-exact copy of the owner's rows: IDENTICAL again
     fused     + fused RowParallelLinear all-reduce (edit A7) as well -- hidden states differ from NCCL's by one bf16
               rounding per layer, so tokens are compared as a match fraction of the first generated tokens
-Prints one JSON line; exit code 0 iff `vp` == `nccl` token for token.
+Prints one JSON line; exit code 0 iff `vp` and `emb` == `nccl` token for token.
 """
 from __future__ import annotations
 
@@ -23,9 +24,10 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 ARMS = {
-    "nccl": {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "0"},
-    "vp": {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "1"},
-    "fused": {"NVLLM_FUSED_ALLREDUCE": "1", "NVLLM_VOCAB_PARALLEL_SAMPLER": "1"},
+    "nccl": {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "0", "NVLLM_FUSED_EMBEDDING": "0"},
+    "vp": {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "1", "NVLLM_FUSED_EMBEDDING": "0"},
+    "emb": {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "1", "NVLLM_FUSED_EMBEDDING": "1"},
+    "fused": {"NVLLM_FUSED_ALLREDUCE": "1", "NVLLM_VOCAB_PARALLEL_SAMPLER": "1", "NVLLM_FUSED_EMBEDDING": "1"},
 }
 
 
@@ -99,7 +101,7 @@ def main():
     if args.out:
         with open(args.out, "w") as f:
             json.dump(dict(line, tokens={a: r.get("tokens") for a, r in res.items()}), f)
-    ok = base is not None and res.get("vp", {}).get("tokens") == base
+    ok = base is not None and all(res[a].get("tokens") == base for a in ("vp", "emb") if a in res)
     sys.exit(0 if ok else 1)
 
 

@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,memory.total --format=csv > gpurun_out/r02_tp${N}_gpus.txt 2>&1
 nvidia-smi topo -m >> gpurun_out/r02_tp${N}_gpus.txt 2>&1
 timeout 700 python -m pytest tests/test_gpu_rowparallel.py tests/test_gpu_rowparallel_worlds.py tests/test_gpu_multi_device.py \
-    tests/test_gpu_sampler_sharded.py tests/test_gpu_engine_tp.py -q -m gpu --timeout 300 --maxfail 6 > gpurun_out/r02_tp${N}_tests.log 2>&1
+    tests/test_gpu_sampler_sharded.py tests/test_gpu_vocab_embedding.py tests/test_gpu_engine_tp.py -q -m gpu --timeout 300 --maxfail 6 > gpurun_out/r02_tp${N}_tests.log 2>&1
 echo "tests rc=$?"; tail -12 gpurun_out/r02_tp${N}_tests.log | cut -c1-300
 if [ -z "$LEAN" ]; then
   timeout 600 python tools/check_tp_tokens.py --tensor-parallel-size $N --layers 28 --steps 64 --port 2480 \

@@ -3,7 +3,7 @@
     python tools/make_integration.py [--src baseline/_ref] [--dst /tmp/nvllm_integration/nanovllm_cuda]
 
 Copies `<src>/nanovllm` to `<dst>/nanovllm` (under the system temp directory by default, never inside the repository) and applies exactly the
-edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5-A8), plus two environment-compat
+edits a maintainer would make to admit `--attn-backend cuda` (A1-A4, and the optional fusions A5-A9), plus two environment-compat
 edits (C1-C2) that have nothing to do with the backend but are needed for the unmodified reference
 to construct under this image's transformers 5.5 and network setup.  Every edit is an
 anchored string replacement that must match exactly once; the flash/triton/sdpa code paths are not
@@ -78,6 +78,17 @@ EDITS = [
      '        load_model(self.model, config.model)\n'
      '        from nano_vllm_learn_b200 import sampler_cuda as _vocab_parallel   # A8: only with the cuda backend\n'
      '        _vocab_parallel.configure(attn_backend == "cuda")\n'),
+    # ---- A9 (third collective; optional: NVLLM_FUSED_EMBEDDING=0 keeps masked lookup + dist.all_reduce):
+    #      VocabParallelEmbedding lookup + row exchange in one launch over NVLink peer memory for <= 512 tokens
+    #      (nanovllm/layers/embed_head.py:35-43)
+    ("nanovllm/layers/embed_head.py", None,
+     'from nano_vllm_learn_b200.embedding_cuda import install as _install_fused_embedding\n'
+     '_install_fused_embedding(VocabParallelEmbedding)\n'),
+    ("nanovllm/engine/model_runner.py",
+     '        torch.set_default_dtype(hf_config.torch_dtype)\n',
+     '        torch.set_default_dtype(hf_config.torch_dtype)\n'
+     '        from nano_vllm_learn_b200 import embedding_cuda as _fused_embedding   # A9: only with the cuda backend\n'
+     '        _fused_embedding.configure(attn_backend == "cuda")\n'),
     # ---- C1: transformers>=5 exposes rope parameters as a dict even for the default rope
     ("nanovllm/config.py",
      '        self.hf_config = AutoConfig.from_pretrained(self.model)\n',
