@@ -34,7 +34,8 @@ def engine_max_tokens(in_features_per_rank: int, out_features: int, world: int =
     if world >= 4:
         # round 2, 4 B200s (profiles/r02_bench_n4.json): every shard 1.1-1.5x at 64 tokens, 0.64-0.96x at 256 -- the
         # one-shot exchange pushes world-1 fp32 copies, so the break-even moves down as the world grows
-        return 128 if wbytes <= (4 << 20) else 64
+        # 8 B200s (profiles/r02_bench_n8.json): 1.3-1.65x at 64 tokens, 0.72-1.07x at 256 on every shard
+        return 64 if world >= 8 else (128 if wbytes <= (4 << 20) else 64)
     return 256 if wbytes <= (4 << 20) else 64 if wbytes <= (16 << 20) else 32
 
 
@@ -172,8 +173,9 @@ _ENABLED = False
 # NVLLM_FUSED_ALLREDUCE: "1" fused kernel, "0" the reference's F.linear + NCCL all_reduce.  Unset: fused at the world
 # sizes where the FINAL kernel (flag-in-data exchange) passed tests/test_gpu_rowparallel*.py on B200s and bench.py's
 # fused_allreduce leg reported parity_ok: 2 GPUs (profiles/r02_tp2_tests.log, r02_bench_n2.json) and 4 GPUs
-# (profiles/r02_tp4_tests.log, r02_bench_n4.json).  Other world sizes opt in with "1".
-VALIDATED_WORLDS = (2, 4)
+# (profiles/r02_tp4_tests.log, r02_bench_n4.json) and 8 GPUs (profiles/r02_tp8_tests.log: 118 tests, r02_bench_n8.json).
+# Other world sizes opt in with "1".
+VALIDATED_WORLDS = (2, 4, 8)
 
 
 def configure(cuda_backend: bool) -> None:
