@@ -531,6 +531,12 @@ constexpr int kMaxDecodeSmem = 226 * 1024;   // 227 KB opt-in limit minus the ke
 template <class Cfg>
 static int pick_cluster(const DecodeParams& p, int bs, int hkv) {
   if (p.num_splits <= 1 || g_force_cluster == 1) return 1;
+  // Automatic mode: the in-cluster merge only pays when one or two (sequence, kv head) items are cut into >= 64 splits
+  // (ctx 32768, 4q/1kv tp=8 shard: 12.1 vs 12.8 us at bs 1, 13.9 vs 14.5 at bs 2).  With 4-32 items and 4-32 splits the
+  // workspace + last-arriver combine is faster -- 32q/8kv bs 1/2/4: 27.7 / 46.5 / 84.8 us vs 29.6 / 48.9 / 85.8 us in a
+  // cluster; 4q/1kv bs 4: 17.9 vs 18.8 (profiles/r02_decode_sweep_c5.jsonl) -- cluster placement delays the ramp of a
+  // one-wave grid by more than the merge saves.
+  if (g_force_cluster == 0 && p.num_splits < 64) return 1;
   const int64_t ctas = static_cast<int64_t>(p.num_splits) * hkv * bs;
   if (ctas > sm_count_cached()) return 1;
   struct Seen { int dev, c, g, n; };
