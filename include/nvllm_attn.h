@@ -489,6 +489,10 @@ NVLLM_API int nvllm_rowparallel_plan(int32_t n_tokens, int32_t in_features_per_r
 /* tuning / tests: force plan fields (0, 0, -1 = automatic) and the peer timeout (<= 0 keeps it) */
 NVLLM_API int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit,
                                int32_t mode, int64_t timeout_ms);
+/* Token count from which the GEMM half runs on the tcgen05 tensor cores (swap-AB tile: 128 output features x 64|128
+ * tokens, accumulator in TMEM) instead of the mma.sync tile; needs out_features % 128 == 0.  <= 0 = never.  Must be the
+ * same on every rank (the plan is part of the exchange layout).  Env NVLLM_RP_TC_MIN_TOKENS sets the initial value. */
+NVLLM_API int nvllm_rowparallel_set_tc_min_tokens(int32_t min_tokens);
 
 /* Measurement and debug aids (read-bandwidth probe, prefill trace buffer) are not
  * part of this ABI: include/nvllm_tools.h, built into lib/libnvllm_tools.so. */

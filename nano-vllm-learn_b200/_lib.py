@@ -64,6 +64,7 @@ SIGNATURES = {
                                                    c_int32, c_int32, c_void_p]),
     "nvllm_rowparallel_plan": (c_int, [c_int32, c_int32, c_int32, c_int32, _P32, _P32, _P32]),
     "nvllm_rowparallel_set_plan": (c_int, [c_int32, c_int32, c_int32, c_int64]),
+    "nvllm_rowparallel_set_tc_min_tokens": (c_int, [c_int32]),
     "nvllm_advance_decode_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int32,
                                            c_int32, _P32, _P32, _P32, c_int32, c_int32, c_int32, c_void_p]),
     "nvllm_advance_decode_state_max_patches": (c_int32, []),

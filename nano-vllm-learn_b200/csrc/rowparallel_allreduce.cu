@@ -28,6 +28,14 @@
 //   These words live in a region of their own -- anchored at the END of each parity, while the fp32 inboxes and the
 //   two-shot result area of every other plan grow from its start, and nvllm_rowparallel_comm_layout sizes the buffer
 //   so the two never meet -- zeroed at allocation, so nothing but an older epoch can ever sit there.
+// Token batches above 64 (prefill chunks, large decode batches) run step 1 on the 5th-generation tensor cores instead
+// ("swap-AB" tcgen05 tile, template flag TC): A = 128 output features of W (UMMA M = 128), B = the 64 or 128 staged
+// token rows of x (UMMA N), both K-major in the 128-byte-swizzled layout the cp.async loader already writes (8-row x
+// 128-byte atoms, 16-byte chunks XOR-ed with the row: exactly what a SWIZZLE_128B shared-memory descriptor reads), one
+// elected thread issues tcgen05.mma.kind::f16 per 16-wide k step, the fp32 accumulator [128 features x tokens] lives
+// in TMEM, tcgen05.commit on a per-stage mbarrier hands the stage back to the loader, and the epilogue reads TMEM with
+// tcgen05.ld (lane = feature) and writes the transposed tile into the same staged [token][feature] layout steps 2-3
+// consume -- so the cluster reduction and all three exchanges are shared with the mma.sync tile.
 // Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
 // epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
 // waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
@@ -42,6 +50,7 @@
 #include <unordered_map>
 
 #include "common.cuh"
+#include "tcgen05.cuh"
 
 namespace nvllm {
 namespace {
@@ -143,10 +152,17 @@ __host__ __device__ constexpr int rp_stages(int bh, int mt, int bk) {
 }
 
 // BH output features x (MT*16) token rows per CTA, BK k elements per pipeline stage.
-template <int BH, int BK, int MT>
+// tcgen05 tile: ring depth that keeps the CTA under ~100 KB (two CTAs per SM; each allocates <= 128 TMEM columns)
+__host__ __device__ constexpr int rp_tc_stages(int mt) { return mt >= 8 ? 3 : 4; }
+
+template <int BH, int BK, int MT, bool TC = false>
 __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  constexpr int STAGES = rp_stages(BH, MT, BK);
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  // UMMA descriptors with 128-byte swizzle want 1024-byte aligned tiles: the TC launcher over-allocates 1 KiB
+  uint8_t* const smem = TC ? reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023))
+                           : smem_raw;
+  static_assert(!TC || (BH == 128 && BK == 64 && (MT == 4 || MT == 8)), "tcgen05 tile: 128 features x 64|128 tokens x k64");
+  constexpr int STAGES = TC ? rp_tc_stages(MT) : rp_stages(BH, MT, BK);
   constexpr int NT = MT * 16;             // staged token rows (rows past the last token are zero-filled)
   // warp grid: 4 warps split the BH features (decode tiles), or 2 x 2 over (token tiles, features) for 64-feature
   // tiles with >= 32 tokens -- each A fragment then feeds 4 MMAs and each B fragment MT/2, which halves the
@@ -201,6 +217,69 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     }
   };
 
+  float* const ep = reinterpret_cast<float*>(smem);
+  if constexpr (TC) {
+    // ---- tcgen05 path: cp.async ring -> UMMA (one elected thread) -> TMEM accumulator -> staged fp32 tile
+    __shared__ __align__(8) uint64_t tc_bars[STAGES + 1];   // [s]: MMAs reading stage s retired; [STAGES]: all retired
+    __shared__ uint32_t tc_tmem_slot;
+    constexpr uint32_t TMEM_COLS = NT <= 64 ? 64 : 128;
+    constexpr uint32_t IDESC = tc::make_idesc_bf16(BH, NT, /*b_mn_major=*/false);
+    if (tid == 0) {
+#pragma unroll
+      for (int s = 0; s <= STAGES; ++s) tc::mbar_init(smem_u32(&tc_bars[s]), 1);
+      tc::fence_barrier_init();
+    }
+    if (warp == 0) {
+      tc::tmem_alloc(smem_u32(&tc_tmem_slot), TMEM_COLS);
+      tc::tmem_relinquish();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tc_tmem_slot);
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; ++s) {
+      if (s < nk) load_stage(s);
+      cp_async_commit();
+    }
+    for (int i = 0; i < nk; ++i) {
+      cp_async_wait<STAGES - 2>();
+      tc::fence_proxy_async_smem();   // this thread's cp.async writes -> visible to the tensor core's async proxy
+      __syncthreads();                // stage i landed for every thread
+      if (tid == 0) {
+        tc::fence_after_sync();
+        const uint32_t sb = sbase + (i % STAGES) * STAGE_BYTES;
+        const uint64_t da = tc::make_smem_desc(sb, 16, 1024), db = tc::make_smem_desc(sb + W_STAGE, 16, 1024);
+#pragma unroll
+        for (int ks16 = 0; ks16 < BK / 16; ++ks16)   // +32 bytes per k16 step inside the swizzle atom
+          tc::mma_ss(tmem, da + 2 * ks16, db + 2 * ks16, IDESC, (i > 0 || ks16 > 0) ? 1u : 0u);
+        tc::mma_commit(smem_u32(&tc_bars[i % STAGES]));
+      }
+      if (i + STAGES - 1 < nk) {
+        // stage (i-1) % STAGES is refilled: its MMAs (issued one iteration ago) must have retired
+        if (i > 0) tc::mbar_wait(smem_u32(&tc_bars[(i - 1) % STAGES]), static_cast<uint32_t>(((i - 1) / STAGES) & 1));
+        load_stage(i + STAGES - 1);
+      }
+      cp_async_commit();
+    }
+    cp_async_wait<0>();
+    if (tid == 0) tc::mma_commit(smem_u32(&tc_bars[STAGES]));
+    tc::mbar_wait(smem_u32(&tc_bars[STAGES]), 0);   // every MMA retired: the accumulator is final and the ring is free
+    tc::fence_after_sync();
+    __syncthreads();
+    // epilogue: warp w owns TMEM lanes (= features) 32w..32w+31; 32 token columns per tcgen05.ld
+#pragma unroll
+    for (int c0 = 0; c0 < NT; c0 += 32) {
+      uint32_t r[32];
+      tc::tmem_ld32(tmem + (static_cast<uint32_t>(warp * 32) << 16) + static_cast<uint32_t>(c0), r);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) ep[(c0 + j) * EP_STRIDE + warp * 32 + lane] = __uint_as_float(r[j]);
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, TMEM_COLS);
+  } else {
   const int wm = warp / WN, wn = warp % WN;
   float acc[MW][NJ][4];
 #pragma unroll
@@ -249,7 +328,6 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
   cp_async_wait<0>();
   __syncthreads();   // the ring is free: reuse it to stage the fp32 tile [NT][EP_STRIDE]
 
-  float* const ep = reinterpret_cast<float*>(smem);
   {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
@@ -262,6 +340,7 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
       }
     }
   }
+  }   // !TC
   // every CTA of the cluster has staged its k-split partial (release/acquire at cluster scope covers the
   // distributed-shared-memory reads below)
   cluster_arrive();
@@ -445,6 +524,8 @@ struct RpPlan {
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
+constexpr int RP_TC_DEFAULT_MIN_TOKENS = 256;   // see rp_plan; 0 = tcgen05 tile only when forced
+int g_tc_min_tokens = -1;   // tcgen05 tile from this many tokens up; -1 = not read yet (env NVLLM_RP_TC_MIN_TOKENS)
 std::unordered_map<void*, size_t> g_comm_bytes;   // buffers from nvllm_tp_comm_alloc (reset clears them whole)
 int g_force_bk = -1;   // tuning only: NVLLM_RP_BK=64|128 (read once)
 unsigned long long g_timeout_ns = 20ull * 1000 * 1000 * 1000;
@@ -487,6 +568,8 @@ int rp_bk(int bh, int mt, int k_per_rank) {
 }
 
 size_t rp_smem_bytes(int bh, int mt, int bk) {
+  if (bh == 128)   // tcgen05 tile: ring of (128 W rows + mt*16 token rows) x 128 bytes, + 1 KiB to align it to 1024
+    return size_t(rp_tc_stages(mt)) * (size_t(128) + mt * 16) * 128 + 1024;
   const size_t ring = size_t(rp_stages(bh, mt, bk)) * (size_t(bh) + mt * 16) * bk * 2;
   const size_t epi = size_t(mt) * 16 * (bh + 8) * 4;
   return ring > epi ? ring : epi;
@@ -501,6 +584,9 @@ const void* rp_kernel_m(int mt) {
 }
 
 const void* rp_kernel(int bh, int bk, int mt) {
+  if (bh == 128)
+    return mt >= 8 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<128, 64, 8, true>)
+                   : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<128, 64, 4, true>);
   if (bh == 32) return bk == 128 ? rp_kernel_m<32, 128>(mt) : rp_kernel_m<32, 64>(mt);
   return bk == 128 ? rp_kernel_m<64, 128>(mt) : rp_kernel_m<64, 64>(mt);
 }
@@ -524,6 +610,12 @@ cudaError_t rp_warm_device() {
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, bk, mt));
         if (e != cudaSuccess) return e;
       }
+  for (int mt = 4; mt <= 8; mt *= 2) {   // the two tcgen05 instantiations
+    cudaFuncAttributes fa;
+    e = cudaFuncSetAttribute(rp_kernel(128, 64, mt), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(128, 64, mt));
+    if (e != cudaSuccess) return e;
+  }
   if (dev < 64) done[dev] = true;
   return cudaSuccess;
 }
@@ -547,12 +639,12 @@ void rp_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int n_
 // call whose shape was seen before (the eager warm-up before graph capture) issues no CUDA runtime call besides the
 // launch itself.
 int rp_max_clusters(int bh, int mt, int bk, size_t smem, int ksplit, int* out) {
-  static int cache[64][2][2][4][4] = {};
+  static int cache[64][3][2][4][4] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return record_cuda_error(e);
   const int lg = ksplit == 1 ? 0 : ksplit == 2 ? 1 : ksplit == 4 ? 2 : 3;
-  int* slot = dev < 64 ? &cache[dev][bh == 64][bk == 128][mt == 1 ? 0 : mt == 2 ? 1 : mt == 4 ? 2 : 3][lg] : nullptr;
+  int* slot = dev < 64 ? &cache[dev][bh == 128 ? 2 : bh == 64][bk == 128][mt == 1 ? 0 : mt == 2 ? 1 : mt == 4 ? 2 : 3][lg] : nullptr;
   if (slot && *slot > 0) {
     *out = *slot;
     return NVLLM_OK;
@@ -592,7 +684,27 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   const int tiles64 = (out_features / 64) * tok_blocks;
   const bool wide = n_tokens > 64 || (n_tokens > 32 && tiles64 * ksplit_for(tiles64) >= 128);
   int bh = (!wide && (out_features / 32) * tok_blocks <= cap) ? 32 : 64;
+  // tcgen05 tile (128 features x 64|128 tokens) from g_tc_min_tokens tokens up: above that the mma.sync tile is bound by
+  // its shared-memory reads and instruction issue, not by streaming W
+  if (g_tc_min_tokens < 0) {   // first use: NVLLM_RP_TC_MIN_TOKENS overrides the built-in threshold (0 = never)
+    const char* e = getenv("NVLLM_RP_TC_MIN_TOKENS");
+    const int v = e ? atoi(e) : RP_TC_DEFAULT_MIN_TOKENS;
+    g_tc_min_tokens = v <= 0 ? (1 << 30) : (v < 33 ? 33 : v);
+  }
+  // measured on B200 (profiles/r02_rowparallel_local_tile{64,128}.jsonl, GEMM half): the tcgen05 tile wins from 256 tokens
+  // on every 8B-shape shard (37.0 vs 44.7 us, 62.4 vs 80.7 us at 256 / 512 tokens on the 50 MB down_proj shard) and from
+  // 128 tokens where k per rank is long (23.2 vs 26.4 us); on short-k shards at 128 tokens the mma.sync tile is level
+  // Small shards stay on the mma.sync tile at any token count: 128-feature tiles leave them too few CTAs (0.6B o_proj,
+  // 256 tokens, 2 GPUs: 19.2 us vs 13.3 us end to end, profiles/r02_bench_n2_tc_small_shards_REJECTED.json).
+  const bool big_shard = static_cast<int64_t>(k_per_rank) * out_features >= (int64_t(8) << 20);
+  if (out_features % 128 == 0 && big_shard &&
+      (n_tokens >= g_tc_min_tokens || (n_tokens >= g_tc_min_tokens / 2 && k_per_rank >= 4096)))
+    bh = 128;
   if (g_force_bh == 32 || g_force_bh == 64) bh = g_force_bh;
+  if (g_force_bh == 128) {
+    if (out_features % 128 || n_tokens <= 32) return NVLLM_ERR_UNSUPPORTED;   // the tile stages >= 64 token rows
+    bh = 128;
+  }
   const int h_tiles = out_features / bh, n_tiles = h_tiles * tok_blocks;
   if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
   int ksplit = ksplit_for(n_tiles);
@@ -600,8 +712,9 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
     ksplit = g_force_ksplit;
     if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK_MIN) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
   }
-  const int mt = rp_mt(n_tokens);
-  int bk = rp_bk(bh, mt, k_per_rank);
+  int mt = rp_mt(n_tokens);
+  if (bh == 128 && mt < 4) mt = 4;
+  int bk = bh == 128 ? 64 : rp_bk(bh, mt, k_per_rank);
   if ((k_per_rank / ksplit) % bk) bk = 64;
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
   const size_t pushed = size_t(world - 1) * n_tokens * out_features * 4;
@@ -642,7 +755,7 @@ int nvllm_rowparallel_comm_layout(int32_t world, int32_t max_tokens, int32_t in_
   size_t reg = 0, ll = 0;
   bool any = false;
   for (int n = 1; n <= max_tokens; ++n)
-    for (int bh = 32; bh <= 64; bh += 32) {
+    for (int bh = 32; bh <= 128; bh *= 2) {
       RpPlan pl;
       g_force_bh = bh;
       if (rp_plan(n, in_features_per_rank, out_features, world, &pl) != NVLLM_OK) continue;
@@ -653,7 +766,7 @@ int nvllm_rowparallel_comm_layout(int32_t world, int32_t max_tokens, int32_t in_
   g_force_bh = saved_bh;
   if (!any) return NVLLM_ERR_UNSUPPORTED;
   if (header_bytes_out) *header_bytes_out = RP_DATA_OFF;
-  if (regular_bytes_out) *regular_bytes_out = reg;
+  if (regular_bytes_out) *regular_bytes_out = reg + 16;   // the launcher keeps 16 bytes of slack per parity
   if (flag_in_data_bytes_out) *flag_in_data_bytes_out = ll;
   return NVLLM_OK;
 }
@@ -757,13 +870,18 @@ int nvllm_rowparallel_poll_error(uint32_t* error_out, int32_t clear) {
 }
 
 int nvllm_rowparallel_set_plan(int32_t feature_tile, int32_t ksplit, int32_t mode, int64_t timeout_ms) {
-  if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64)) return NVLLM_ERR_BAD_ARG;
+  if (!(feature_tile == 0 || feature_tile == 32 || feature_tile == 64 || feature_tile == 128)) return NVLLM_ERR_BAD_ARG;
   if (ksplit < 0 || ksplit > RP_MAX_KSPLIT || (ksplit & (ksplit - 1))) return NVLLM_ERR_BAD_ARG;
   if (mode < -1 || mode > 3) return NVLLM_ERR_BAD_ARG;   // 2: local partial only (profiling), 3: flag-in-data
   g_force_bh = feature_tile;
   g_force_ksplit = ksplit;
   g_force_mode = mode;
   if (timeout_ms > 0) g_timeout_ns = static_cast<unsigned long long>(timeout_ms) * 1000000ull;
+  return NVLLM_OK;
+}
+
+int nvllm_rowparallel_set_tc_min_tokens(int32_t min_tokens) {
+  g_tc_min_tokens = min_tokens <= 0 ? (1 << 30) : (min_tokens < 33 ? 33 : min_tokens);
   return NVLLM_OK;
 }
 

@@ -126,6 +126,30 @@ def test_token_counts_and_strided_rows(comms, n):
         assert (o[:, :8] == 7).all() and (o[:, 8 + h:] == 7).all()
 
 
+@pytest.mark.parametrize("mode", [0, 1, 3])
+@pytest.mark.parametrize("n", [33, 64, 128, 200, 512])
+def test_tcgen05_tile_through_every_exchange(comms, n, mode):
+    """The swap-AB tcgen05 tile (feature tile 128) feeds the same staged-tile exchanges as the mma.sync tile: one-shot
+    flagged (0), two-shot (1) and flag-in-data (3), ragged token counts over 1-4 token blocks, with a bias."""
+    from nano_vllm_learn_b200 import ops
+    g = torch.Generator().manual_seed(700 + n)
+    k, h = 2048, 1024
+    x = torch.randn(n, k, generator=g).to(torch.bfloat16)
+    w = (torch.randn(h, k, generator=g) * k ** -0.5).to(torch.bfloat16)
+    b = torch.randn(h, generator=g).to(torch.bfloat16)
+    xs, ws = rpo.shard_inputs(x, w, 2)
+    xd = [xs[r].to(f"cuda:{r}") for r in range(2)]
+    wd = [ws[r].to(f"cuda:{r}") for r in range(2)]
+    bd = [b.to(f"cuda:{r}") for r in range(2)]
+    ops.rowparallel_set_plan(128, 0, mode)
+    try:
+        assert ops.rowparallel_plan(n, k // 2, h, 2)[0] == 128
+        ys = _run_world(comms, xd, wd, bd)
+    finally:
+        ops.rowparallel_set_plan(0, 0, -1)
+    _check(ys, xs, ws, b, comms, f"tcgen05 n={n} mode={mode}")
+
+
 def test_back_to_back_calls_alternate_buffers(comms):
     """40 calls with changing inputs, shapes and modes and no host synchronisation: the device-side epoch, the
     double-buffered inboxes and stale flags from other tile geometries."""

@@ -93,3 +93,30 @@ def test_gemm_half_strided_rows_multiple_token_blocks_and_determinism(local_comm
     assert torch.equal(a.view(torch.int16), b.view(torch.int16)), "same inputs, same launch plan -> same bits"
     from nano_vllm_learn_b200.rowparallel_cuda import poll_error
     assert poll_error() == 0
+
+
+@pytest.mark.parametrize("n", [33, 64, 65, 100, 128, 200, 256, 512])      # 64- and 128-token UMMA N, 1-4 token blocks
+@pytest.mark.parametrize("k,h", [(1024, 256), (960, 256), (2048, 1024)])
+def test_gemm_half_tcgen05_tile(local_comm, n, k, h):
+    """The swap-AB tcgen05 tile (feature tile 128: A = 128 output features of W, B = 64|128 token rows, accumulator in
+    TMEM, operands through the same cp.async ring in the 128-byte-swizzled layout) against fp64, same bar."""
+    from nano_vllm_learn_b200 import ops
+    ops.rowparallel_set_plan(128, 0, 2)
+    assert ops.rowparallel_plan(n, k, h, 2)[0] == 128
+    y = _check(ops, local_comm, n, k, h, bias=(n % 2 == 0), seed=n * 3 + k)
+    # and bit-level agreement class with the mma.sync tile: both accumulate in fp32 and round once
+    ops.rowparallel_set_plan(64, 0, 2)
+    y2 = _check(ops, local_comm, n, k, h, bias=(n % 2 == 0), seed=n * 3 + k)
+    assert (y.float() - y2.float()).abs().max().item() <= 2 * ULP * y2.float().abs().max().item()
+
+
+@pytest.mark.parametrize("ksplit", [1, 2, 4, 8])
+def test_gemm_half_tcgen05_cluster_ksplit(local_comm, ksplit):
+    from nano_vllm_learn_b200 import ops
+    ops.rowparallel_set_plan(128, ksplit, 2)
+    _check(ops, local_comm, 96, 2048, 1024, bias=True, seed=400 + ksplit)
+    if ksplit <= 4:   # 2 token blocks x 8 feature tiles x 8-CTA clusters exceed the co-resident cluster capacity
+        _check(ops, local_comm, 130, 2048, 1024, bias=False, seed=500 + ksplit, x_pad=64)
+    ops.rowparallel_set_plan(0, 0, 2)
+    from nano_vllm_learn_b200.rowparallel_cuda import poll_error
+    assert poll_error() == 0

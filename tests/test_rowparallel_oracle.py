@@ -64,7 +64,10 @@ def test_comm_bytes_and_plan_are_host_arithmetic(lib):
         for world, k, h in [(2, 1024, 1024), (2, 2048, 4096), (8, 512, 4096)]:
             assert lib.nvllm_rowparallel_plan(n, k, h, world, ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)) == 0
             tiles = (h // bh.value) * ((n + 127) // 128)
-            assert bh.value in (32, 64) and ks.value in (1, 2, 4, 8) and mode.value in (0, 1, 3)
+            assert bh.value in (32, 64, 128) and ks.value in (1, 2, 4, 8) and mode.value in (0, 1, 3)
+            # the tcgen05 tile (128 features) only from 256 tokens up (128 where k per rank >= 4096)
+            # and only on shards of >= 8 Mi elements (small shards would be left with too few CTAs)
+            assert (bh.value == 128) == (n >= 256 and h % 128 == 0 and k * h >= (8 << 20))
             assert tiles * ks.value <= 296, "grid must fit one co-resident wave (2 CTAs x 148 SMs)"
             assert k % (ks.value * 64) == 0
     assert lib.nvllm_rowparallel_plan(513, 1024, 1024, 2, None, None, None) == 2
@@ -73,6 +76,17 @@ def test_comm_bytes_and_plan_are_host_arithmetic(lib):
     assert lib.nvllm_rowparallel_set_plan(48, 0, -1, 0) == 1
     assert lib.nvllm_rowparallel_set_plan(0, 3, -1, 0) == 1
     assert lib.nvllm_rowparallel_set_plan(0, 0, 4, 0) == 1   # 2: local-partial profiling mode, 3: flag-in-data one-shot
+    assert lib.nvllm_rowparallel_set_plan(128, 0, -1, 0) == 0
+    assert lib.nvllm_rowparallel_plan(16, 1024, 1024, 2, None, None, None) == 2     # the tcgen05 tile stages >= 64 token rows
+    assert lib.nvllm_rowparallel_plan(64, 1024, 1024, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
+    assert lib.nvllm_rowparallel_set_tc_min_tokens(0) == 0
+    assert lib.nvllm_rowparallel_set_plan(0, 0, -1, 0) == 0
+    assert lib.nvllm_rowparallel_plan(512, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
+    assert lib.nvllm_rowparallel_set_tc_min_tokens(256) == 0
+    assert lib.nvllm_rowparallel_plan(512, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
+    assert lib.nvllm_rowparallel_plan(512, 1024, 1024, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
+    assert lib.nvllm_rowparallel_plan(128, 4096, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
+    assert lib.nvllm_rowparallel_plan(128, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
     assert lib.nvllm_rowparallel_set_plan(64, 2, 1, 0) == 0
     assert lib.nvllm_rowparallel_plan(16, 1024, 1024, 2, ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)) == 0
     assert (bh.value, ks.value, mode.value) == (64, 2, 1)

@@ -1,4 +1,6 @@
-timeout 200 python tools/sweep_decode.py --shapes c4 --variants -1 --splits 0,1,2,4,8,16 --clusters 0 > gpurun_out/r02_decode_sweep_c4.jsonl 2>&1; echo "c4 rc=$?"
-timeout 200 python tools/sweep_decode.py --shapes c5all --variants -1 --flash --clusters 0,1 > gpurun_out/r02_decode_sweep_c5.jsonl 2>&1; echo "c5 rc=$?"
-timeout 200 python tools/sweep_prefill.py --impls tcgen05 --flash > gpurun_out/r02_prefill_sweep.jsonl 2>&1; echo "prefill rc=$?"
-cut -c1-260 gpurun_out/r02_decode_sweep_c4.jsonl | tail -30
+timeout 300 python -m pytest tests/test_gpu_rowparallel_local.py -m gpu -x -q --timeout 120 > gpurun_out/r02_rp_tc_tests.log 2>&1; echo "tests rc=$?"
+tail -15 gpurun_out/r02_rp_tc_tests.log | cut -c1-300
+for tile in 64 128; do
+  timeout 200 python tools/bench_rowparallel_local.py --tile $tile --tokens 64 128 256 512 --only 8b --iters 5 > gpurun_out/r02_rowparallel_local_tile${tile}.jsonl 2>&1; echo "bench tile $tile rc=$?"
+  cut -c1-420 gpurun_out/r02_rowparallel_local_tile${tile}.jsonl | tail -14
+done

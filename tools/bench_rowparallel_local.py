@@ -59,6 +59,9 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--ncu", action="store_true")
+    ap.add_argument("--tile", type=int, default=0, help="force the feature tile: 32 | 64 (mma.sync) | 128 (tcgen05)")
+    ap.add_argument("--tokens", type=int, nargs="+", default=[1, 16, 32, 64, 128, 256])
+    ap.add_argument("--only", default="", help="substring filter on the shape name")
     a = ap.parse_args()
     from nano_vllm_learn_b200 import ops
     from nano_vllm_learn_b200.rowparallel_cuda import TPComm
@@ -68,7 +71,7 @@ def main():
               ("qwen3-8b o_proj tp2", 2048, 4096), ("qwen3-8b down_proj tp2", 6144, 4096),
               ("qwen3-8b down_proj tp8", 1536, 4096)]
     comm = make_comm(TPComm.required_bytes(2, [(k, h) for _, k, h in shapes]))
-    ops.rowparallel_set_plan(0, 0, 2)
+    ops.rowparallel_set_plan(a.tile, 0, 2)
     g = torch.Generator().manual_seed(0)
     if a.ncu:
         k, h, n = 6144, 4096, 16
@@ -81,13 +84,15 @@ def main():
         return
     rows = []
     for name, k, h in shapes:
+        if a.only and a.only not in name:
+            continue
         wbytes = k * h * 2
         ncopies = max(2, -(-(320 << 20) // wbytes))
         ncopies = min(ncopies, 160)
         ws = [(torch.randn(h, k, generator=g) * k ** -0.5).to(torch.bfloat16).to(dev) for _ in range(min(ncopies, 4))]
         while len(ws) < ncopies:          # distinct memory, repeated values
             ws.append(ws[len(ws) % 4].clone())
-        for n in (1, 16, 32, 64, 128, 256):
+        for n in a.tokens:
             x = torch.randn(n, k, generator=g).to(torch.bfloat16).to(dev)
             y = torch.empty(n, h, dtype=torch.bfloat16, device=dev)
             got = ops.rowparallel_linear_allreduce(x, ws[0], None, comm).float()
