@@ -25,6 +25,7 @@ struct PrefillParams {
   int32_t total_q;  // rows of q / out
   int32_t total_k;  // dense: rows of k/v; paged: num_blocks * block_size
   float scale_log2;
+  int32_t pair_heads;  // tcgen05 kernel: the two query tiles of a work item are two q heads of one kv head (else two row blocks)
 };
 
 // prefill_tcgen05.cu: returns NVLLM_OK and sets *handled when it launched the tcgen05 kernel.

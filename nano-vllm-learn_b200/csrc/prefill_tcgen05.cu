@@ -70,8 +70,15 @@ enum Bar : int {
 // Work item = (sequence, q head, pair of query tiles).  Items are enumerated heavy-first (late pairs see
 // the most keys under the causal mask) and adjacent ids share the sequence and kv head, so CTAs running
 // side by side hit the same K/V tiles in L2.  Every role of a CTA decodes the same item the same way.
+// The two query tiles of an item are either two consecutive 128-row blocks of ONE q head (row pairing) or the SAME
+// 128 rows of two q heads that share the kv head (head pairing, p.pair_heads; needs an even GQA group).  Head pairing
+// gives both tiles the same K/V tiles AND the same causal mask, so n_t[0] == n_t[1]: with row pairing tile B always
+// runs one KV tile more than A, and that last tile has no partner to ping-pong with -- 1 of only 2-8 tiles per item
+// at 1024-token prompts.
 struct Item {
   int seq, h, kvh, q0, k0, Lq, Lk, m0, shift, n_t[2], n_tiles;
+  int mr[2];   // first query row (inside the sequence) of tile t
+  int hq[2];   // q head of tile t
   bool live;
 };
 
@@ -80,32 +87,44 @@ struct Item {
 // busiest CTA carried 29 % more than the mean, 4 % this way).
 __device__ __forceinline__ Item decode_item(const PrefillParams& p, int slot, int num_pairs, int batch) {
   Item it;
-  const int per_pair = p.num_q_heads * batch;
+  const int heads = p.pair_heads ? p.num_q_heads / 2 : p.num_q_heads;   // head slots per (row tile | tile pair, sequence)
+  const int per_pair = heads * batch;
   const int grid = static_cast<int>(gridDim.x);
   const int round = slot / grid, cta = slot % grid;
   const int w = round * grid + ((round & 1) ? grid - 1 - cta : cta);
   if (w >= num_pairs * per_pair) {   // the last round may be partial
     it.seq = it.h = it.kvh = it.q0 = it.k0 = it.Lq = it.Lk = it.m0 = it.shift = it.n_tiles = 0;
     it.n_t[0] = it.n_t[1] = 0;
+    it.mr[0] = it.mr[1] = it.hq[0] = it.hq[1] = 0;
     it.live = false;
     return it;
   }
   const int mbp = num_pairs - 1 - w / per_pair;
   const int rem = w % per_pair;
-  it.seq = rem / p.num_q_heads;
-  it.h = rem % p.num_q_heads;
+  it.seq = rem / heads;
+  it.h = p.pair_heads ? 2 * (rem % heads) : rem % heads;
   it.kvh = it.h / p.group;
   it.q0 = __ldg(p.cu_q + it.seq);
   it.Lq = __ldg(p.cu_q + it.seq + 1) - it.q0;
   it.k0 = __ldg(p.cu_k + it.seq);
   it.Lk = __ldg(p.cu_k + it.seq + 1) - it.k0;
-  it.m0 = mbp * 2 * TM;
+  it.m0 = p.pair_heads ? mbp * TM : mbp * 2 * TM;
   it.shift = it.Lk - it.Lq;
   it.live = it.m0 < it.Lq;
+  it.mr[0] = it.m0;
+  it.hq[0] = it.h;
   const int hiA = min(it.Lk, it.shift + it.m0 + TM);
   it.n_t[0] = (it.live && hiA > 0) ? (hiA + TN - 1) / TN : 0;
-  const int hiB = (it.m0 + TM < it.Lq) ? min(it.Lk, it.shift + it.m0 + 2 * TM) : 0;
-  it.n_t[1] = (it.live && hiB > 0) ? (hiB + TN - 1) / TN : 0;
+  if (p.pair_heads) {
+    it.mr[1] = it.m0;
+    it.hq[1] = it.h + 1;
+    it.n_t[1] = it.n_t[0];
+  } else {
+    it.mr[1] = it.m0 + TM;
+    it.hq[1] = it.h;
+    const int hiB = (it.m0 + TM < it.Lq) ? min(it.Lk, it.shift + it.m0 + 2 * TM) : 0;
+    it.n_t[1] = (it.live && hiB > 0) ? (hiB + TN - 1) / TN : 0;
+  }
   it.n_tiles = max(it.n_t[0], it.n_t[1]);
   it.live = it.live && it.n_tiles > 0;
   return it;
@@ -226,8 +245,8 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
           const uint32_t sq = smem + kSmemQ + t * kTileBytes;
           if (lead) {
             tc::mbar_arrive_expect_tx(bar(kQFull + t), kTileBytes);
-            tc::tma_load_2d(sq, &tm_q, it.h * kHeadDim, it.q0 + it.m0 + t * TM, bar(kQFull + t));
-            tc::tma_load_2d(sq + kHalfBytes, &tm_q, it.h * kHeadDim + 64, it.q0 + it.m0 + t * TM, bar(kQFull + t));
+            tc::tma_load_2d(sq, &tm_q, it.hq[t] * kHeadDim, it.q0 + it.mr[t], bar(kQFull + t));
+            tc::tma_load_2d(sq + kHalfBytes, &tm_q, it.hq[t] * kHeadDim + 64, it.q0 + it.mr[t], bar(kQFull + t));
           }
           __syncwarp();
         }
@@ -423,6 +442,11 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
   *handled = false;
   if (p.total_q <= 0 || p.total_k <= 0) return NVLLM_OK;  // caller did not give TMA bounds: use the mma.sync kernel
   if (p.block_tables && p.block_size % TN != 0) return NVLLM_OK;
+  // pair the two query tiles of a work item by GQA head whenever the group allows it (NVLLM_PREFILL_PAIR=rows keeps
+  // the round-1 pairing of two consecutive row blocks of one head; read per call so sweeps can flip it)
+  PrefillParams pp = p;
+  const char* pair_env = getenv("NVLLM_PREFILL_PAIR");
+  pp.pair_heads = (p.group % 2 == 0 && !(pair_env && pair_env[0] == 'r')) ? 1 : 0;
   CUtensorMap tq, tk, tv;
   const uint64_t kv_cols = static_cast<uint64_t>(p.num_kv_heads) * kHeadDim;
   if (!make_map(&tq, p.q, static_cast<uint64_t>(p.num_q_heads) * kHeadDim, p.total_q, p.q_row_stride)) return NVLLM_OK;
@@ -454,12 +478,12 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
   cudaError_t e0 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
 #endif
   if (e0 != cudaSuccess) return record_cuda_error(e0);
-  const int num_pairs = (max_seqlen_q + 2 * TM - 1) / (2 * TM);
-  const int64_t total = static_cast<int64_t>(num_pairs) * p.num_q_heads * batch;
+  const int num_pairs = pp.pair_heads ? (max_seqlen_q + TM - 1) / TM : (max_seqlen_q + 2 * TM - 1) / (2 * TM);
+  const int64_t total = static_cast<int64_t>(num_pairs) * (pp.pair_heads ? pp.num_q_heads / 2 : pp.num_q_heads) * batch;
   if (total > INT32_MAX) return NVLLM_ERR_UNSUPPORTED;
   const int sms = device_sm_count();
   const unsigned grid = static_cast<unsigned>(total < sms ? total : sms);   // persistent: one CTA per SM
-  kernel<<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, p, num_pairs, batch, debug);
+  kernel<<<grid, kThreads, kSmemBytes, stream>>>(tq, tk, tv, pp, num_pairs, batch, debug);
   note_launch();
   *handled = true;
   return record_cuda_error(cudaGetLastError());

@@ -60,7 +60,7 @@
         const uint32_t s_addr = tmem + lane_base + static_cast<uint32_t>(t * TN + grp * CG);
         const uint32_t p_addr = tmem + lane_base + static_cast<uint32_t>(t * TN + grp * (CG / 2));  // bf16 pairs over S_t
         const uint32_t o_addr = tmem + lane_base + 2u * TN + static_cast<uint32_t>(t * kHeadDim + grp * CG);
-        const int qrow = it.m0 + t * TM + row;              // row inside the sequence
+        const int qrow = it.mr[t] + row;              // row inside the sequence
         const int limit = min(it.shift + qrow, it.Lk - 1);  // last visible key of this row
         const bool dump = kDebug && debug != nullptr && it.m0 == 0 && it.h == 0 && it.seq == 0 && t == 0;
         if (tr) trace_stamp(debug, 1 + t, j, 0);
@@ -83,7 +83,7 @@
 #pragma unroll
           for (int i = 0; i < CG; ++i) debug[row * TN + grp * CG + i] = __uint_as_float(s[i]);
         }
-        const bool need_mask = (j * TN + TN - 1 > it.shift + it.m0 + t * TM) || (j * TN + TN > it.Lk);
+        const bool need_mask = (j * TN + TN - 1 > it.shift + it.mr[t]) || (j * TN + TN > it.Lk);
         if (need_mask) {
 #pragma unroll
           for (int i = 0; i < CG; ++i)
@@ -182,7 +182,7 @@
       const int nt = it.n_t[t];
       if (nt == 0) continue;
       const uint32_t o_addr = tmem + lane_base + 2u * TN + static_cast<uint32_t>(t * kHeadDim + grp * CG);
-      const int qrow = it.m0 + t * TM + row;
+      const int qrow = it.mr[t] + row;
       const bool dump = kDebug && debug != nullptr && it.m0 == 0 && it.h == 0 && it.seq == 0 && t == 0;
       const float l_all = exchange(l_run[tt], false);
       tc::mbar_wait(bar(kOFull + t), o_cnt[tt] & 1u);
@@ -205,7 +205,7 @@
       // 32 rows x 32 columns at a time through its private staging rows (80 B pitch: conflict-free 16-byte writes), so a
       // store instruction covers 8 rows x 64 contiguous bytes.
       unsigned char* const stg = smem_gen + kSmemStage + warp * (32 * kStagePitch);
-      const int r0 = it.m0 + t * TM + (warp & 3) * 32;      // first row of this warp inside the sequence
+      const int r0 = it.mr[t] + (warp & 3) * 32;      // first row of this warp inside the sequence
 #pragma unroll
       for (int pass = 0; pass < CG / 32; ++pass) {
 #pragma unroll
@@ -224,7 +224,7 @@
           const int r = i * 8 + (lane >> 2);
           const uint4 v = *reinterpret_cast<const uint4*>(stg + r * kStagePitch + (lane & 3) * 16);
           if (r0 + r < it.Lq) {
-            __nv_bfloat16* dst = p.out + (static_cast<int64_t>(it.q0 + r0 + r) * p.num_q_heads + it.h) * kHeadDim +
+            __nv_bfloat16* dst = p.out + (static_cast<int64_t>(it.q0 + r0 + r) * p.num_q_heads + it.hq[t]) * kHeadDim +
                                  grp * CG + pass * 32 + (lane & 3) * 8;
             *reinterpret_cast<uint4*>(dst) = v;
           }

@@ -288,6 +288,7 @@ int nvllm_varlen_prefill(void* out, const void* q, int64_t q_row_stride, const v
     return NVLLM_ERR_ALIGNMENT;
 
   PrefillParams p;
+  p.pair_heads = 0;   // chosen by the tcgen05 launcher
   p.q = static_cast<const __nv_bfloat16*>(q);
   p.q_row_stride = q_row_stride;
   p.k = static_cast<const __nv_bfloat16*>(k);

@@ -1,6 +1,5 @@
-timeout 300 python -m pytest tests/test_gpu_rowparallel_local.py -m gpu -x -q --timeout 120 > gpurun_out/r02_rp_tc_tests.log 2>&1; echo "tests rc=$?"
-tail -15 gpurun_out/r02_rp_tc_tests.log | cut -c1-300
-for tile in 64 128; do
-  timeout 200 python tools/bench_rowparallel_local.py --tile $tile --tokens 64 128 256 512 --only 8b --iters 5 > gpurun_out/r02_rowparallel_local_tile${tile}.jsonl 2>&1; echo "bench tile $tile rc=$?"
-  cut -c1-420 gpurun_out/r02_rowparallel_local_tile${tile}.jsonl | tail -14
-done
+timeout 300 python -m pytest tests/test_gpu_prefill_tcgen05.py tests/test_gpu_parity.py -m gpu -x -q -k "prefill or prefix" --timeout 120 > gpurun_out/r02_prefill_pair_tests.log 2>&1; echo "tests rc=$?"
+tail -4 gpurun_out/r02_prefill_pair_tests.log | cut -c1-300
+timeout 200 python tools/sweep_prefill.py --impls tcgen05 > gpurun_out/r02_prefill_sweep_pair_heads.jsonl 2>&1; echo "heads rc=$?"
+NVLLM_PREFILL_PAIR=rows timeout 200 python tools/sweep_prefill.py --impls tcgen05 > gpurun_out/r02_prefill_sweep_pair_rows.jsonl 2>&1; echo "rows rc=$?"
+echo HEADS; cut -c1-160 gpurun_out/r02_prefill_sweep_pair_heads.jsonl; echo ROWS; cut -c1-160 gpurun_out/r02_prefill_sweep_pair_rows.jsonl
