@@ -757,7 +757,7 @@ def run_fused_allreduce(args, dev, rank, world, ops, dist):
 
     for name, k, h in shapes:
         kr = k // world
-        for n in (1, 16, 64, 256):
+        for n in (1, 16, 64, 128, 256, 512):
             gen = torch.Generator(device=dev).manual_seed(7000 + 13 * n + k + rank)
             x = torch.empty(n, kr, dtype=torch.bfloat16, device=dev).normal_(generator=gen)
             w = (torch.empty(h, kr, dtype=torch.float32, device=dev).normal_(generator=gen) * k ** -0.5).to(torch.bfloat16)
@@ -787,6 +787,7 @@ def run_fused_allreduce(args, dev, rank, world, ops, dist):
                 row["hbm_floor_us"] = round(wbytes / (peaks()[0] * 1e3), 2)
                 row["nvlink_push_bytes"] = push
                 row["nvlink_floor_us_at_770GBps"] = round(push / 770e3, 2)
+                row["plan_feature_tile_ksplit_mode"] = list(ops.rowparallel_plan(n, kr, h, world))   # tile 128 = tcgen05
             rows.append(row)
     torch.cuda.synchronize()
     dist.barrier()

@@ -28,14 +28,17 @@
 //   These words live in a region of their own -- anchored at the END of each parity, while the fp32 inboxes and the
 //   two-shot result area of every other plan grow from its start, and nvllm_rowparallel_comm_layout sizes the buffer
 //   so the two never meet -- zeroed at allocation, so nothing but an older epoch can ever sit there.
-// Token batches above 64 (prefill chunks, large decode batches) run step 1 on the 5th-generation tensor cores instead
-// ("swap-AB" tcgen05 tile, template flag TC): A = 128 output features of W (UMMA M = 128), B = the 64 or 128 staged
-// token rows of x (UMMA N), both K-major in the 128-byte-swizzled layout the cp.async loader already writes (8-row x
-// 128-byte atoms, 16-byte chunks XOR-ed with the row: exactly what a SWIZZLE_128B shared-memory descriptor reads), one
-// elected thread issues tcgen05.mma.kind::f16 per 16-wide k step, the fp32 accumulator [128 features x tokens] lives
-// in TMEM, tcgen05.commit on a per-stage mbarrier hands the stage back to the loader, and the epilogue reads TMEM with
-// tcgen05.ld (lane = feature) and writes the transposed tile into the same staged [token][feature] layout steps 2-3
-// consume -- so the cluster reduction and all three exchanges are shared with the mma.sync tile.
+// Token batches from 64-128 up on big shards run step 1 on the 5th-generation tensor cores instead ("swap-AB" tcgen05
+// tile, template flag TC): A = 128 output features of W (UMMA M = 128), B = 128 token rows of x (UMMA N), both K-major
+// with 128-byte swizzle.  Warp 0 is the TMA producer (one elected lane: two cp.async.bulk.tensor.2d per 64-wide k stage
+// into a 6-stage, 192 KB ring, mbarrier complete_tx; token rows past n are out of the tensor map's bounds and arrive as
+// zeros), warp 1 the MMA issuer (one elected lane: four tcgen05.mma.kind::f16 per stage, tcgen05.commit hands the
+// stage back), the fp32 accumulator [128 features x 128 tokens] lives in TMEM, and all four warps read it with
+// tcgen05.ld (lane = feature) and write the transposed tile into the same staged [token][feature] layout steps 2-3
+// consume -- so the cluster reduction and all three exchanges are shared with the mma.sync tile.  One CTA per SM.
+// The first cut fed the UMMA from the cp.async ring (same swizzled layout): LSU request tracking capped it near
+// 5 TB/s of L2+HBM traffic however deep the ring (profiles/r02_rowparallel_local_tile128_tcgen05_cpasync_v1.jsonl,
+// r02_rowparallel_tcgen05_n256_ncu_full_metrics.csv); bulk copies took the 50 MB shard at 256 tokens from 37 to 24 us.
 // Flags carry a call epoch kept in device memory (graph replays advance it), data areas are double-buffered by
 // epoch parity; nothing is reset, nothing is allocated per call.  A pushed store never waits on anything, so a
 // waiting CTA only depends on CTAs that cannot block before publishing; the launcher additionally keeps the grid
@@ -88,6 +91,9 @@ struct RpParams {
   unsigned long long ll_off;      // offset of the flag-in-data inbox inside a parity (mode 3)
   unsigned long long timeout_ns;
   uint32_t* host_err;             // mapped pinned host word: a timeout is visible to the host without a sync
+  // tcgen05 tile only: TMA descriptors of W [out, k/tp] and x [n, k/tp] (box 128 rows x 64 k, 128-byte swizzle)
+  alignas(64) CUtensorMap tm_w;
+  alignas(64) CUtensorMap tm_x;
 };
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
@@ -152,16 +158,20 @@ __host__ __device__ constexpr int rp_stages(int bh, int mt, int bk) {
 }
 
 // BH output features x (MT*16) token rows per CTA, BK k elements per pipeline stage.
-// tcgen05 tile: ring depth that keeps the CTA under ~100 KB (two CTAs per SM; each allocates <= 128 TMEM columns)
-__host__ __device__ constexpr int rp_tc_stages(int mt) { return mt >= 8 ? 3 : 4; }
+// tcgen05 tile: ONE CTA per SM with a 192 KB ring (6 stages of 16 KB W + 16 KB x), filled by TMA.  ncu of the first cut (3 stages, two
+// CTAs per SM by shared memory, profiles/r02_rowparallel_tcgen05_n256_ncu_full_metrics.csv): the cluster capacity
+// halved the k split, 128 CTAs of 4 warps ran one per SM with 64 KB in flight each and DRAM sat at 1.35 TB/s -- the
+// tile is bound by bytes in flight per SM, not by the tensor pipe (19 % active), so depth goes to the ring.
+__host__ __device__ constexpr int rp_tc_stages(int /*mt*/) { return 6; }
+constexpr int RP_TC_PLAN_CAP = 148;   // co-resident CTAs of the tcgen05 tile (one per SM)
 
 template <int BH, int BK, int MT, bool TC = false>
-__global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const RpParams p) {
+__global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const __grid_constant__ RpParams p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   // UMMA descriptors with 128-byte swizzle want 1024-byte aligned tiles: the TC launcher over-allocates 1 KiB
   uint8_t* const smem = TC ? reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023))
                            : smem_raw;
-  static_assert(!TC || (BH == 128 && BK == 64 && (MT == 4 || MT == 8)), "tcgen05 tile: 128 features x 64|128 tokens x k64");
+  static_assert(!TC || (BH == 128 && BK == 64 && MT == 8), "tcgen05 tile: 128 features x 128 tokens x k64 per stage");
   constexpr int STAGES = TC ? rp_tc_stages(MT) : rp_stages(BH, MT, BK);
   constexpr int NT = MT * 16;             // staged token rows (rows past the last token are zero-filled)
   // warp grid: 4 warps split the BH features (decode tiles), or 2 x 2 over (token tiles, features) for 64-feature
@@ -219,15 +229,21 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
 
   float* const ep = reinterpret_cast<float*>(smem);
   if constexpr (TC) {
-    // ---- tcgen05 path: cp.async ring -> UMMA (one elected thread) -> TMEM accumulator -> staged fp32 tile
-    __shared__ __align__(8) uint64_t tc_bars[STAGES + 1];   // [s]: MMAs reading stage s retired; [STAGES]: all retired
+    // ---- tcgen05 path: TMA ring -> UMMA (one elected thread each) -> TMEM accumulator -> staged fp32 tile
+    __shared__ __align__(8) uint64_t tc_full[STAGES], tc_empty[STAGES], tc_done;
     __shared__ uint32_t tc_tmem_slot;
-    constexpr uint32_t TMEM_COLS = NT <= 64 ? 64 : 128;
+    constexpr uint32_t TMEM_COLS = 128;
     constexpr uint32_t IDESC = tc::make_idesc_bf16(BH, NT, /*b_mn_major=*/false);
     if (tid == 0) {
 #pragma unroll
-      for (int s = 0; s <= STAGES; ++s) tc::mbar_init(smem_u32(&tc_bars[s]), 1);
+      for (int s = 0; s < STAGES; ++s) {
+        tc::mbar_init(smem_u32(&tc_full[s]), 1);
+        tc::mbar_init(smem_u32(&tc_empty[s]), 1);
+      }
+      tc::mbar_init(smem_u32(&tc_done), 1);
       tc::fence_barrier_init();
+      tc::tma_prefetch_desc(&p.tm_w);
+      tc::tma_prefetch_desc(&p.tm_x);
     }
     if (warp == 0) {
       tc::tmem_alloc(smem_u32(&tc_tmem_slot), TMEM_COLS);
@@ -237,34 +253,40 @@ __global__ void __launch_bounds__(RP_THREADS) rowparallel_allreduce_kernel(const
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(&tc_tmem_slot);
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) {
-      if (s < nk) load_stage(s);
-      cp_async_commit();
-    }
-    for (int i = 0; i < nk; ++i) {
-      cp_async_wait<STAGES - 2>();
-      tc::fence_proxy_async_smem();   // this thread's cp.async writes -> visible to the tensor core's async proxy
-      __syncthreads();                // stage i landed for every thread
-      if (tid == 0) {
-        tc::fence_after_sync();
-        const uint32_t sb = sbase + (i % STAGES) * STAGE_BYTES;
-        const uint64_t da = tc::make_smem_desc(sb, 16, 1024), db = tc::make_smem_desc(sb + W_STAGE, 16, 1024);
-#pragma unroll
-        for (int ks16 = 0; ks16 < BK / 16; ++ks16)   // +32 bytes per k16 step inside the swizzle atom
-          tc::mma_ss(tmem, da + 2 * ks16, db + 2 * ks16, IDESC, (i > 0 || ks16 > 0) ? 1u : 0u);
-        tc::mma_commit(smem_u32(&tc_bars[i % STAGES]));
+    const int k_begin = ks * p.kc;
+    if (warp == 0) {
+      // producer: one lane feeds the ring with two bulk tensor copies per stage (W tile + x tile; rows of x past the
+      // last token are out of bounds of the tensor map and arrive as zeros).  Bulk copies need no LSU request
+      // tracking, so the whole 192 KB ring is in flight (the cp.async loader saturated near 5 TB/s of L2+HBM traffic).
+      if (tc::elect_one()) {
+        for (int i = 0; i < nk; ++i) {
+          const int s = i % STAGES;
+          if (i >= STAGES) tc::mbar_wait(smem_u32(&tc_empty[s]), static_cast<uint32_t>((i / STAGES - 1) & 1));
+          const uint32_t full = smem_u32(&tc_full[s]);
+          const uint32_t dst = sbase + s * STAGE_BYTES;
+          tc::mbar_arrive_expect_tx(full, STAGE_BYTES);
+          tc::tma_load_2d(dst, &p.tm_w, k_begin + i * BK, ht * BH, full);
+          tc::tma_load_2d(dst + W_STAGE, &p.tm_x, k_begin + i * BK, tok0, full);
+        }
       }
-      if (i + STAGES - 1 < nk) {
-        // stage (i-1) % STAGES is refilled: its MMAs (issued one iteration ago) must have retired
-        if (i > 0) tc::mbar_wait(smem_u32(&tc_bars[(i - 1) % STAGES]), static_cast<uint32_t>(((i - 1) / STAGES) & 1));
-        load_stage(i + STAGES - 1);
+    } else if (warp == 1) {
+      if (tc::elect_one()) {
+        for (int i = 0; i < nk; ++i) {
+          const int s = i % STAGES;
+          tc::mbar_wait(smem_u32(&tc_full[s]), static_cast<uint32_t>((i / STAGES) & 1));
+          tc::fence_after_sync();
+          const uint32_t sb = sbase + s * STAGE_BYTES;
+          const uint64_t da = tc::make_smem_desc(sb, 16, 1024), db = tc::make_smem_desc(sb + W_STAGE, 16, 1024);
+#pragma unroll
+          for (int ks16 = 0; ks16 < BK / 16; ++ks16)   // +32 bytes per k16 step inside the swizzle atom
+            tc::mma_ss(tmem, da + 2 * ks16, db + 2 * ks16, IDESC, (i > 0 || ks16 > 0) ? 1u : 0u);
+          tc::mma_commit(smem_u32(&tc_empty[s]));   // the stage may be refilled once these MMAs have retired
+        }
+        tc::mma_commit(smem_u32(&tc_done));
       }
-      cp_async_commit();
     }
-    cp_async_wait<0>();
-    if (tid == 0) tc::mma_commit(smem_u32(&tc_bars[STAGES]));
-    tc::mbar_wait(smem_u32(&tc_bars[STAGES]), 0);   // every MMA retired: the accumulator is final and the ring is free
+    __syncwarp();
+    tc::mbar_wait(smem_u32(&tc_done), 0);   // every MMA retired: the accumulator is final and the ring is free
     tc::fence_after_sync();
     __syncthreads();
     // epilogue: warp w owns TMEM lanes (= features) 32w..32w+31; 32 token columns per tcgen05.ld
@@ -524,7 +546,7 @@ struct RpPlan {
 };
 
 int g_force_bh = 0, g_force_ksplit = 0, g_force_mode = -1;
-constexpr int RP_TC_DEFAULT_MIN_TOKENS = 256;   // see rp_plan; 0 = tcgen05 tile only when forced
+constexpr int RP_TC_DEFAULT_MIN_TOKENS = 128;   // see rp_plan; 0 = tcgen05 tile only when forced
 int g_tc_min_tokens = -1;   // tcgen05 tile from this many tokens up; -1 = not read yet (env NVLLM_RP_TC_MIN_TOKENS)
 std::unordered_map<void*, size_t> g_comm_bytes;   // buffers from nvllm_tp_comm_alloc (reset clears them whole)
 int g_force_bk = -1;   // tuning only: NVLLM_RP_BK=64|128 (read once)
@@ -569,7 +591,7 @@ int rp_bk(int bh, int mt, int k_per_rank) {
 
 size_t rp_smem_bytes(int bh, int mt, int bk) {
   if (bh == 128)   // tcgen05 tile: ring of (128 W rows + mt*16 token rows) x 128 bytes, + 1 KiB to align it to 1024
-    return size_t(rp_tc_stages(mt)) * (size_t(128) + mt * 16) * 128 + 1024;
+    return size_t(rp_tc_stages(mt)) * (size_t(128) + 128) * 128 + 1024;
   const size_t ring = size_t(rp_stages(bh, mt, bk)) * (size_t(bh) + mt * 16) * bk * 2;
   const size_t epi = size_t(mt) * 16 * (bh + 8) * 4;
   return ring > epi ? ring : epi;
@@ -584,9 +606,7 @@ const void* rp_kernel_m(int mt) {
 }
 
 const void* rp_kernel(int bh, int bk, int mt) {
-  if (bh == 128)
-    return mt >= 8 ? reinterpret_cast<const void*>(rowparallel_allreduce_kernel<128, 64, 8, true>)
-                   : reinterpret_cast<const void*>(rowparallel_allreduce_kernel<128, 64, 4, true>);
+  if (bh == 128) return reinterpret_cast<const void*>(rowparallel_allreduce_kernel<128, 64, 8, true>);
   if (bh == 32) return bk == 128 ? rp_kernel_m<32, 128>(mt) : rp_kernel_m<32, 64>(mt);
   return bk == 128 ? rp_kernel_m<64, 128>(mt) : rp_kernel_m<64, 64>(mt);
 }
@@ -610,10 +630,10 @@ cudaError_t rp_warm_device() {
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(bh, bk, mt));
         if (e != cudaSuccess) return e;
       }
-  for (int mt = 4; mt <= 8; mt *= 2) {   // the two tcgen05 instantiations
+  {   // the tcgen05 instantiation
     cudaFuncAttributes fa;
-    e = cudaFuncSetAttribute(rp_kernel(128, 64, mt), cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
-    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(128, 64, mt));
+    e = cudaFuncSetAttribute(rp_kernel(128, 64, 8), cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(128, 64, 8));
     if (e != cudaSuccess) return e;
   }
   if (dev < 64) done[dev] = true;
@@ -670,7 +690,7 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
   if (n_tokens <= 0 || n_tokens > RP_MAX_TOKENS || world < 2 || world > RP_MAX_WORLD) return NVLLM_ERR_UNSUPPORTED;
   if (k_per_rank <= 0 || k_per_rank % RP_BK_MIN || out_features <= 0 || out_features % 64) return NVLLM_ERR_UNSUPPORTED;
   const int tok_blocks = (n_tokens + RP_TOKB - 1) / RP_TOKB;
-  const int cap = RP_PLAN_CAP;
+  int cap = RP_PLAN_CAP;
   // 64-feature tiles (2 x 2 warp grid, half the x re-reads) above 32 tokens when they still give >= 128 CTAs, and
   // always above 64 tokens or when 32-feature tiles would not fit one wave
   auto ksplit_for = [&](int tiles) {
@@ -691,20 +711,23 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
     const int v = e ? atoi(e) : RP_TC_DEFAULT_MIN_TOKENS;
     g_tc_min_tokens = v <= 0 ? (1 << 30) : (v < 33 ? 33 : v);
   }
-  // measured on B200 (profiles/r02_rowparallel_local_tile{64,128}.jsonl, GEMM half): the tcgen05 tile wins from 256 tokens
-  // on every 8B-shape shard (37.0 vs 44.7 us, 62.4 vs 80.7 us at 256 / 512 tokens on the 50 MB down_proj shard) and from
-  // 128 tokens where k per rank is long (23.2 vs 26.4 us); on short-k shards at 128 tokens the mma.sync tile is level
+  // measured on B200, GEMM half alone (profiles/r02_rowparallel_local_tile64_mma_sync.jsonl vs
+  // r02_rowparallel_local_tile128_tcgen05_tma.jsonl), 8B-shape down_proj shard (50 MB) at 64 / 128 / 256 / 512 tokens:
+  // 16.1 / 17.5 / 23.7 / 35.7 us against 19.1 / 26.4 / 44.7 / 80.7 us for the mma.sync tile (cuBLAS alone: 12.2 / 12.7 /
+  // 14.2 / 20.7); o_proj shard (16 MB): 10.6 / 12.4 / 15.6 / 20.2 vs 10.3 / 13.4 / 19.9 / 32.7.  So: from 128 tokens on
+  // every big shard, from 64 where k per rank is long.
   // Small shards stay on the mma.sync tile at any token count: 128-feature tiles leave them too few CTAs (0.6B o_proj,
   // 256 tokens, 2 GPUs: 19.2 us vs 13.3 us end to end, profiles/r02_bench_n2_tc_small_shards_REJECTED.json).
   const bool big_shard = static_cast<int64_t>(k_per_rank) * out_features >= (int64_t(8) << 20);
-  if (out_features % 128 == 0 && big_shard &&
+  if (out_features % 128 == 0 && big_shard && (out_features / 128) * tok_blocks <= RP_TC_PLAN_CAP &&
       (n_tokens >= g_tc_min_tokens || (n_tokens >= g_tc_min_tokens / 2 && k_per_rank >= 4096)))
     bh = 128;
   if (g_force_bh == 32 || g_force_bh == 64) bh = g_force_bh;
   if (g_force_bh == 128) {
-    if (out_features % 128 || n_tokens <= 32) return NVLLM_ERR_UNSUPPORTED;   // the tile stages >= 64 token rows
+    if (out_features % 128 || n_tokens <= 32) return NVLLM_ERR_UNSUPPORTED;   // pointless below a few MMA rows
     bh = 128;
   }
+  if (bh == 128) cap = RP_TC_PLAN_CAP;
   const int h_tiles = out_features / bh, n_tiles = h_tiles * tok_blocks;
   if (n_tiles > RP_MAX_TILES || n_tiles > cap) return NVLLM_ERR_UNSUPPORTED;
   int ksplit = ksplit_for(n_tiles);
@@ -713,7 +736,7 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
     if (ksplit > RP_MAX_KSPLIT || k_per_rank % (ksplit * RP_BK_MIN) || n_tiles * ksplit > cap) return NVLLM_ERR_UNSUPPORTED;
   }
   int mt = rp_mt(n_tokens);
-  if (bh == 128 && mt < 4) mt = 4;
+  if (bh == 128) mt = 8;   // the tcgen05 tile always stages 128 token rows (UMMA N = 128; TMA zero-fills the rest)
   int bk = bh == 128 ? 64 : rp_bk(bh, mt, k_per_rank);
   if ((k_per_rank / ksplit) % bk) bk = 64;
   // one-shot while the fp32 partials a rank pushes over NVLink stay small; else reduce-scatter + all-gather
@@ -942,6 +965,14 @@ int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride, const void
   p.ll_off = (p.par_bytes - pl.ll_need) / 16 * 16;   // end-anchored: see rp_plan
   p.timeout_ns = g_timeout_ns;
   p.host_err = rp_host_error_word();
+  if (pl.bh == 128) {
+    // TMA descriptors of this call's operands (host-side encode, ~1 us each; baked into a captured graph's node)
+    if (!tc::make_tile_map_bf16(&p.tm_w, weight, static_cast<uint64_t>(in_features_per_rank),
+                                static_cast<uint64_t>(out_features), static_cast<uint64_t>(w_row_stride)) ||
+        !tc::make_tile_map_bf16(&p.tm_x, x, static_cast<uint64_t>(in_features_per_rank), static_cast<uint64_t>(n_tokens),
+                                static_cast<uint64_t>(x_row_stride)))
+      return NVLLM_ERR_UNSUPPORTED;
+  }
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr;
   rp_launch_config(&cfg, &attr, pl.n_tiles * pl.ksplit, pl.ksplit, pl.smem, static_cast<cudaStream_t>(stream));

@@ -20,10 +20,9 @@ import torch
 from . import _lib, ops
 
 MAX_TOKENS = 512          # nvllm_rowparallel_linear_allreduce's n_tokens limit (include/nvllm_attn.h (6))
-# Batches the engine hands to the fused kernel, by weight-shard size.  Measured on 2 and 4 B200s against cuBLAS + NCCL
-# (profiles/r01_rowparallel_tp2_v4_flag_in_data.jsonl, r01_rowparallel_tp4_v3_static_tiles.jsonl): Qwen3-0.6B shards
-# (2-3 MiB) 2.1-2.5x up to 64 tokens and 1.3-1.4x up to 256; 8B-shape o_proj (16 MiB) 1.1-2.1x up to 64; 8B-shape
-# down_proj (50 MiB) 1.2-2.0x up to 32 and slower from 64 on.  Larger batches keep the reference's own forward.
+# Batches the engine hands to the fused kernel, by weight-shard size and world size: the largest token count at which the
+# fused kernel still beat cuBLAS + NCCL on B200s (bench.py fused_allreduce leg, profiles/r02_bench_n{2,4,8}*.json).
+# Larger batches keep the reference's own forward.
 _ENV_MAX = os.environ.get("NVLLM_FUSED_ALLREDUCE_MAX_TOKENS")
 
 
@@ -36,7 +35,9 @@ def engine_max_tokens(in_features_per_rank: int, out_features: int, world: int =
         # one-shot exchange pushes world-1 fp32 copies, so the break-even moves down as the world grows
         # 8 B200s (profiles/r02_bench_n8.json): 1.3-1.65x at 64 tokens, 0.72-1.07x at 256 on every shard
         return 64 if world >= 8 else (128 if wbytes <= (4 << 20) else 64)
-    return 256 if wbytes <= (4 << 20) else 64 if wbytes <= (16 << 20) else 32
+    # 2 B200s, round 2 with the tcgen05 tile from 64-128 tokens up on big shards (profiles/r02_bench_n2_tcgen05_tile.json):
+    # 0.6B shards 1.04-1.15x at 512 tokens; 8B-shape o_proj / down_proj 1.05x / 1.14x at 128 and 0.97x / 0.92x at 256
+    return 512 if wbytes <= (4 << 20) else 128
 
 
 _IPC_HANDLE_BYTES = 64

@@ -65,9 +65,9 @@ def test_comm_bytes_and_plan_are_host_arithmetic(lib):
             assert lib.nvllm_rowparallel_plan(n, k, h, world, ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)) == 0
             tiles = (h // bh.value) * ((n + 127) // 128)
             assert bh.value in (32, 64, 128) and ks.value in (1, 2, 4, 8) and mode.value in (0, 1, 3)
-            # the tcgen05 tile (128 features) only from 256 tokens up (128 where k per rank >= 4096)
+            # the tcgen05 tile (128 features) only from 128 tokens up (64 where k per rank >= 4096)
             # and only on shards of >= 8 Mi elements (small shards would be left with too few CTAs)
-            assert (bh.value == 128) == (n >= 256 and h % 128 == 0 and k * h >= (8 << 20))
+            assert (bh.value == 128) == (n >= 128 and h % 128 == 0 and k * h >= (8 << 20))
             assert tiles * ks.value <= 296, "grid must fit one co-resident wave (2 CTAs x 148 SMs)"
             assert k % (ks.value * 64) == 0
     assert lib.nvllm_rowparallel_plan(513, 1024, 1024, 2, None, None, None) == 2
@@ -82,11 +82,11 @@ def test_comm_bytes_and_plan_are_host_arithmetic(lib):
     assert lib.nvllm_rowparallel_set_tc_min_tokens(0) == 0
     assert lib.nvllm_rowparallel_set_plan(0, 0, -1, 0) == 0
     assert lib.nvllm_rowparallel_plan(512, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
-    assert lib.nvllm_rowparallel_set_tc_min_tokens(256) == 0
+    assert lib.nvllm_rowparallel_set_tc_min_tokens(128) == 0
     assert lib.nvllm_rowparallel_plan(512, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
     assert lib.nvllm_rowparallel_plan(512, 1024, 1024, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
-    assert lib.nvllm_rowparallel_plan(128, 4096, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
-    assert lib.nvllm_rowparallel_plan(128, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
+    assert lib.nvllm_rowparallel_plan(64, 4096, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 128
+    assert lib.nvllm_rowparallel_plan(64, 2048, 4096, 2, ctypes.byref(bh), None, None) == 0 and bh.value == 64
     assert lib.nvllm_rowparallel_set_plan(64, 2, 1, 0) == 0
     assert lib.nvllm_rowparallel_plan(16, 1024, 1024, 2, ctypes.byref(bh), ctypes.byref(ks), ctypes.byref(mode)) == 0
     assert (bh.value, ks.value, mode.value) == (64, 2, 1)
@@ -131,9 +131,12 @@ def _patch_worker(rank, world, port, q):
         ok = ok0 and m._nvllm_fused and (c["k"] // world, c["h"]) in rowparallel_cuda._SHAPES
         odd = mod.RowParallelLinear(200, 100)          # shape the kernel does not take: stays on the reference path
         ok = ok and not odd._nvllm_fused
-        # the engine hands over batches by shard size (measured crossover vs cuBLAS + NCCL): 3 MiB shard -> 256 tokens
-        ok = ok and m._nvllm_fused_max == 256 and rowparallel_cuda.engine_max_tokens(2048, 4096) == 64 \
-            and rowparallel_cuda.engine_max_tokens(6144, 4096) == 32
+        # the engine hands over batches by shard and world size (measured crossover vs cuBLAS + NCCL): 3 MiB shard at
+        # 2 ranks -> 512 tokens, the 8B-shape shards -> 128; fewer tokens at 4 and 8 ranks
+        ok = ok and m._nvllm_fused_max == 512 and rowparallel_cuda.engine_max_tokens(2048, 4096) == 128 \
+            and rowparallel_cuda.engine_max_tokens(6144, 4096) == 128 \
+            and rowparallel_cuda.engine_max_tokens(1024, 1024, 4) == 128 and rowparallel_cuda.engine_max_tokens(6144, 4096, 4) == 64 \
+            and rowparallel_cuda.engine_max_tokens(1024, 1024, 8) == 64
         # env unset: on at the validated world sizes (2 is one); "0": the reference's collective
         del os.environ["NVLLM_FUSED_ALLREDUCE"]
         rowparallel_cuda.configure(True)

@@ -74,7 +74,7 @@ def main():
     ops.rowparallel_set_plan(a.tile, 0, 2)
     g = torch.Generator().manual_seed(0)
     if a.ncu:
-        k, h, n = 6144, 4096, 16
+        k, h, n = 6144, 4096, a.tokens[0] if a.tile == 128 else 16
         w = (torch.randn(h, k, generator=g) * k ** -0.5).to(torch.bfloat16).to(dev)
         x = torch.randn(n, k, generator=g).to(torch.bfloat16).to(dev)
         y = torch.empty(n, h, dtype=torch.bfloat16, device=dev)

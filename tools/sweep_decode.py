@@ -107,6 +107,8 @@ def main():
         "c5": [(bs, 32768, 32 // tp, 8 // tp, 160, [0, 8, 16, 32, 64]) for bs in (1, 4) for tp in (1, 8)],
         "c5all": [(bs, 32768, 32 // tp, 8 // tp, 160, [0, 16]) for bs in (1, 2, 4) for tp in (1, 8)],
         "head": [(64, 4096, 16, 8, 16, [0, 1])],
+        "c5bs1": [(1, 32768, 32, 8, 160, [0, 12, 14, 16, 18, 20, 24, 32]), (2, 32768, 32, 8, 160, [0, 8, 9, 10, 12, 16]),
+                  (1, 32768, 4, 1, 160, [0, 48, 64, 96, 128])],
         "c4tp1": [(128, 4096, 32, 8, 16, [0])],
         "c4tp8": [(128, 4096, 4, 1, 16, [0])],
     }
