@@ -96,7 +96,11 @@ def test_engine_flash_vs_cuda(tmp_path, fused):
         d = (ka[0, 0].float() - kb[0, 0].float()).abs()
         assert (d <= ka[0, 0].float().abs().amax(dim=-1, keepdim=True) * 2.0 ** -6 + 1e-30).all()
         assert (d > 0).float().mean().item() <= 0.02
-    # deeper layers see attention outputs: bf16 tolerance
+    # Deeper layers see attention outputs.  The per-op bar (north_star: 2e-2 max-abs against the oracle) is asserted on
+    # the attention OUTPUT in tests/test_gpu_parity.py and tests/test_gpu_prefill_tcgen05.py.  Here two different bf16
+    # kernels (flash-attn vs cuda), each inside that bar, feed o_proj + the MLP + the next layer's k/v projections
+    # and norms, which amplify a 1-ulp difference of the attention output: the layer-1 cache and the logits are
+    # compared at 5e-2 (about 2.5 op-level bars), a sanity bound on the composition, not the op's parity bar.
     assert (ka.float() - kb.float()).abs().max().item() <= 5e-2
     la, lb = a["logits"], b["logits"]
     assert la.shape == lb.shape
