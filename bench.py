@@ -963,7 +963,8 @@ def run_vocab_parallel_sampler(args, dev, rank, world, ops, dist):
 def run_tp_e2e(args, world):
     """The metric BASELINE.json names beside the op-level one: bench_my decode tok/s of the reference ENGINE at
     tensor_parallel_size = N (its own spawned ranks, NCCL, scheduler, CUDA graphs), `flash` backend vs `cuda` backend
-    (and `cuda` with the NCCL all-reduce when N > 1), bounded: Qwen3-0.6B random-init, bs 64, input 512, output 128.
+    (and, when N > 1, `cuda` with the reference's NCCL collectives instead of the fused all-reduce / embedding exchange /
+    vocabulary-parallel sampler), bounded: Qwen3-0.6B random-init, bs 64, input 512, output 128.
     Runs tools/bench_my_b200.py as a subprocess of rank 0 after the torchrun ranks have released their GPUs."""
     import signal
     script = os.path.join(ROOT, "tools", "bench_my_b200.py")
@@ -973,14 +974,14 @@ def run_tp_e2e(args, world):
                         "TORCHELASTIC_MAX_RESTARTS", "TORCHELASTIC_USE_AGENT_STORE", "TORCH_NCCL_ASYNC_ERROR_HANDLING",
                         "TORCHELASTIC_ERROR_FILE", "OMP_NUM_THREADS")}
     arms = [("flash", {}), ("cuda", {})]
-    if world > 1:
-        arms.append(("cuda", {"NVLLM_FUSED_ALLREDUCE": "0"}))
+    if world > 1:   # the cuda attention backend with every collective left to the reference's NCCL calls
+        arms.append(("cuda", {"NVLLM_FUSED_ALLREDUCE": "0", "NVLLM_VOCAB_PARALLEL_SAMPLER": "0", "NVLLM_FUSED_EMBEDDING": "0"}))
     out = {"workload": f"reference engine, Qwen3-0.6B random-init, tensor_parallel_size={world}, bs 64, input 512, "
                        f"output 128, temperature 0, ignore_eos (bench_my protocol, tok/s = bs*out/wall)", "arms": []}
     deadline = time.time() + args.tp_e2e_timeout
     for i, (backend, extra) in enumerate(arms):
         left = deadline - time.time()
-        label = backend + ("+nccl_allreduce" if extra else ("+fused_allreduce" if backend == "cuda" and world > 1 else ""))
+        label = backend + ("+nccl_collectives" if extra else ("+fused_collectives" if backend == "cuda" and world > 1 else ""))
         if left < 45:
             out["arms"].append({"arm": label, "skipped": "time budget of the tp_e2e leg spent"})
             continue

@@ -440,6 +440,7 @@ def install(model_runner_cls, set_context: Callable, get_context: Callable, rese
         self.graphs = {}
         self.graph_pool = None
         g.dev.zero_()
+        g._fast = None          # the staging buffer was just cleared: no device-side decode state survives
         for bs in reversed(self.graph_bs):
             ids, pos, slots, lens, tab = g.graph_buffers(bs)
             graph = torch.cuda.CUDAGraph()
