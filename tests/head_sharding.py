@@ -1,10 +1,12 @@
-"""KV-head sharding of the attention path under tensor parallelism.
+"""TEST HELPER (not part of the product package): KV-head sharding of the attention path under tensor parallelism.
 
 Mirrors `Qwen3Attention.__init__` (nanovllm/models/qwen3.py:30-39): with tensor_parallel_size `world`
 each rank owns `Hq / world` query heads and `Hkv / world` kv heads — contiguous ranges, because
 `QKVParallelLinear` slices the fused projection by rank (nanovllm/layers/linear.py).  Attention needs
 no collective: heads are independent and every rank sees identical slot_mapping / block_tables /
-context_lens.
+context_lens.  The product never shards anything itself: the reference's model code hands each rank its heads, and the
+kernels are checked at the sharded shapes on the box (tests/test_gpu_parity.py decode cases g1/g8, bench.py tp_strong,
+tests/test_gpu_engine_tp.py at tensor_parallel_size 2).
 """
 from __future__ import annotations
 

@@ -1,7 +1,11 @@
 """CPU, gloo, world_size 2: the multi-GPU path shards attention by KV head with NO data-path
 collective.  Each rank runs its head shard; gathering the shards along the head axis
 must reproduce the unsharded result bit for bit, and the runner glue must publish identical
-metadata on every rank."""
+metadata on every rank.
+Scope: this is a property of the ALGORITHM (heads are independent), shown on the CPU oracle because no CUDA kernel can run
+here; the product kernels at head-sharded shapes and the engine at tensor_parallel_size 2 are covered on the box
+(tests/test_gpu_parity.py, tests/test_gpu_engine_tp.py, bench.py tp_strong); the host logic of the N > 1 collectives has
+its own gloo world-2 tests (tests/test_rowparallel_oracle.py, tests/test_tp_head_patches_gloo.py)."""
 import os
 import sys
 
@@ -23,7 +27,7 @@ def _worker(rank, world, port, q_out):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        from nano_vllm_learn_b200.sharding import shard_heads
+        from head_sharding import shard_heads
         c = cases.make_decode_case("c1_bs1_ctx512")
         hq, hkv = c["hq"], c["hkv"]
         q_lo, q_hi, kv_lo, kv_hi = shard_heads(rank, world, hq, hkv)
@@ -60,7 +64,7 @@ def test_kv_head_sharding_world2():
 
 
 def test_shard_heads_partition():
-    from nano_vllm_learn_b200.sharding import shard_heads
+    from head_sharding import shard_heads
     for hq, hkv in ((16, 8), (32, 8)):
         for world in (1, 2, 4, 8):
             seen_q, seen_kv = [], []
