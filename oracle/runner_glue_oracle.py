@@ -158,3 +158,25 @@ def find_reference_root() -> Optional[str]:
         if os.path.isdir(os.path.join(cand, "nanovllm")):
             return cand
     return None
+
+
+# ------------------------------------------------------------------ device-side decode state
+def advance_decode_state_ref(state: dict, sampled, patches, pad_cols, block_size: int = 256) -> dict:
+    """What csrc/decode_state.cu does to the published decode tensors between two steps of an UNCHANGED batch, restated
+    on CPU: `state` is the dict prepare_decode_ref returned for the previous step (input_ids, positions, slot_mapping,
+    context_lens, block_tables), `sampled` the token ids sampled in that step, `patches` = [(row, column, block id)] for
+    the blocks BlockManager.may_append opened (block_manager.py:134-159), `pad_cols` = (begin, end) table columns that
+    join the live width this step (they carry the reference's -1 padding, model_runner.py:163-166)."""
+    ids = torch.as_tensor(sampled, dtype=torch.int64).clone()
+    lens = state["context_lens"].clone() + 1
+    tab = state["block_tables"].clone()
+    if pad_cols[1] > tab.shape[1]:
+        tab = torch.cat([tab, torch.zeros(tab.shape[0], pad_cols[1] - tab.shape[1], dtype=tab.dtype)], dim=1)
+    tab[:, pad_cols[0]:pad_cols[1]] = -1
+    for r, c, v in patches:
+        tab[r, c] = v
+    last = lens - 1
+    blk = tab[torch.arange(tab.shape[0]), (last // block_size).long()]
+    slots = (blk * block_size + last % block_size).to(torch.int32)
+    return dict(input_ids=ids, positions=lens.to(torch.int64), slot_mapping=slots, context_lens=lens.to(torch.int32),
+                block_tables=tab)

@@ -205,3 +205,33 @@ def test_live_reference_trace(lib):
             m = gorc.prepare_decode_ref(seqs)
             for k in ("slot_mapping", "context_lens", "block_tables", "positions", "input_ids"):
                 assert torch.equal(m[k], want[k])
+
+
+def test_device_side_advance_restatement_tracks_prepare_decode():
+    """CPU statement of the algorithm behind nvllm_advance_decode_state (the kernel itself is checked on the box,
+    tests/test_gpu_decode_state.py): starting from one staged step, 600 increments with the may_append patches reproduce
+    what prepare_decode builds from the sequences at every step -- including rows crossing block boundaries at the same
+    step and a new column joining the table width."""
+    free = list(range(900, 100, -1))
+
+    def mk(n):
+        s = Seq([1], [free.pop() for _ in range((n + BS - 1) // BS)], 0, n, 1)
+        return s
+    seqs = [mk(n) for n in (250, 3, 511, 250, 700)]
+    state = gorc.prepare_decode_ref(seqs)
+    for step in range(1, 600):
+        toks, patches = [], []
+        width = state["block_tables"].shape[1]
+        for i, s in enumerate(seqs):
+            t = (step * 131 + i * 7) % 10000
+            s.last_token = t
+            s.num_tokens += 1
+            if s.num_tokens % BS == 1:
+                s.block_table.append(free.pop())
+                patches.append((i, len(s.block_table) - 1, s.block_table[-1]))
+            toks.append(t)
+        new_width = max(len(s.block_table) for s in seqs)
+        state = gorc.advance_decode_state_ref(state, toks, patches, (width, new_width), BS)
+        want = gorc.prepare_decode_ref(seqs)
+        for k in ("input_ids", "positions", "slot_mapping", "context_lens", "block_tables"):
+            assert state[k].dtype == want[k].dtype and torch.equal(state[k], want[k]), (step, k)
