@@ -296,7 +296,8 @@ class RunnerGlue:
                                  f_tab.data_ptr(), cols_l)
         rc = self.lib.nvllm_advance_decode_state(ptrs[0], ptrs[1], ptrs[2], ptrs[3], ptrs[4], ptrs[5],
                                                  device_tokens.data_ptr(), bs, bsz, *self._patch_ptrs, n_patch,
-                                                 old_width, width, torch.cuda.current_stream().cuda_stream)
+                                                 old_width, width,
+                                                 torch.cuda.current_stream().cuda_stream if self.pinned else None)
         if rc != 0:
             self._fast = None
             _lib.check(rc, "advance_decode_state")

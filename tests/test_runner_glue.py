@@ -235,3 +235,85 @@ def test_device_side_advance_restatement_tracks_prepare_decode():
         want = gorc.prepare_decode_ref(seqs)
         for k in ("input_ids", "positions", "slot_mapping", "context_lens", "block_tables"):
             assert state[k].dtype == want[k].dtype and torch.equal(state[k], want[k]), (step, k)
+
+
+class _KernelShim:
+    """Stands in for the C library in the host-logic test below: forwards everything to the real library except
+    nvllm_advance_decode_state, which it executes on the (CPU) staging buffer exactly as csrc/decode_state.cu is
+    specified in include/nvllm_attn.h (4b) -- so the HOST side of the device path (what it decides to patch, pad and
+    fall back on) runs in the CPU suite; the kernel itself is tested on the box (tests/test_gpu_decode_state.py)."""
+
+    def __init__(self, real):
+        self._real = real
+        self.calls = 0
+        self.max_patches_seen = 0
+
+    def __getattr__(self, name):
+        return getattr(self._real, name)
+
+    def nvllm_advance_decode_state(self, ids, pos, slots, lens, tab, stride, sampled, bs, bsz, prow, pcol, pval, n_patch,
+                                   pad_lo, pad_hi, stream):
+        import ctypes
+        import numpy as np
+
+        def arr(ptr, n, ct, dt):
+            return np.frombuffer((ct * n).from_address(ptr), dtype=dt)
+        a_ids, a_pos = arr(ids, bs, ctypes.c_int64, np.int64), arr(pos, bs, ctypes.c_int64, np.int64)
+        a_slots, a_lens = arr(slots, bs, ctypes.c_int32, np.int32), arr(lens, bs, ctypes.c_int32, np.int32)
+        a_tab = arr(tab, bs * stride, ctypes.c_int32, np.int32).reshape(bs, stride)
+        a_sampled = arr(sampled, bs, ctypes.c_int64, np.int64)
+        assert 0 <= n_patch <= self._real.nvllm_advance_decode_state_max_patches() and stream is None
+        self.calls += 1
+        self.max_patches_seen = max(self.max_patches_seen, n_patch)
+        a_tab[:, pad_lo:pad_hi] = -1
+        for i in range(n_patch):
+            a_tab[prow[i], pcol[i]] = pval[i]
+        a_lens += 1
+        last = a_lens - 1
+        a_ids[:] = a_sampled
+        a_pos[:] = a_lens
+        a_slots[:] = a_tab[np.arange(bs), last // bsz] * bsz + last % bsz
+        return 0
+
+
+@pytest.mark.parametrize("graphs", [False, True])
+def test_device_side_path_host_logic_on_cpu(lib, graphs):
+    """The glue's decisions on the device-side decode path (patch lists, -1 padding of new columns, fall-backs on layout
+    change / too many patches / changed batch) with the kernel emulated on the CPU staging buffer: every step must
+    publish what the reference's prepare_decode builds."""
+    import itertools
+    ctx = Ctx()
+    g = _glue(lib, ctx, max_num_seqs=64)
+    g.device_state = True                       # normally CUDA-only
+    shim = g.lib = _KernelShim(g.lib)
+    if graphs:
+        g.graph_bs = [1, 2, 4, 8] + list(range(16, 65, 16))
+    free = itertools.count(100)
+    ids = itertools.count()
+
+    def mk(n):
+        s = Seq([1], [next(free) for _ in range((n + BS - 1) // BS)], 0, n, 1)
+        s.seq_id = next(ids)
+        return s
+    # 20 sequences of EQUAL length cross a block boundary at the same step (more patches than one launch carries)
+    seqs = [mk(n) for n in (250, 3, 511, 700)] + [mk(200) for _ in range(20)]
+    g.prepare_decode(seqs, None)
+    for step in range(1, 400):
+        toks = []
+        for i, s in enumerate(seqs):
+            s.last_token = (step * 31 + i) % 10000
+            s.num_tokens += 1
+            if s.num_tokens % BS == 1:
+                s.block_table.append(next(free))
+            toks.append(s.last_token)
+        if step == 300:
+            seqs = seqs[:3] + seqs[5:]         # two sequences finish: rows shift
+            toks = toks[:3] + toks[5:]
+        ids_t, pos_t = g.prepare_decode(seqs, torch.tensor(toks, dtype=torch.int64))
+        want = gorc.prepare_decode_ref(seqs)
+        assert torch.equal(ids_t, want["input_ids"]) and torch.equal(pos_t, want["positions"]), step
+        for k in ("slot_mapping", "context_lens", "block_tables"):
+            got = getattr(ctx.args, k)
+            assert got.dtype == want[k].dtype and torch.equal(got, want[k]), (step, k)
+    assert shim.calls == g.fast_steps and g.fast_steps + g.staged_steps == 400
+    assert g.fast_steps >= 380 and 1 <= shim.max_patches_seen <= 16
