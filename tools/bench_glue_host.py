@@ -73,22 +73,32 @@ def run(bs, steps, ctx, device_state, graphs):
 
 
 def run_reference(bs, steps, ctx):
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    try:
-        from oracle import runner_glue_oracle as gorc   # only to locate + import the unmodified reference module
-        root = gorc.find_reference_root()
-        ref = gorc.ReferenceGlue(root)
-    except Exception as e:
+    """The reference's UNMODIFIED ModelRunner.prepare_decode (nanovllm/engine/model_runner.py:244-269), imported from
+    baseline/_ref (or /root/reference) and called on a stub that carries only block_size -- on the GPU box its pinned
+    tensors and .cuda() copies are the real thing.  None when the reference is not importable."""
+    import importlib
+    import types
+    root = next((r for r in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference")
+                 if os.path.isdir(os.path.join(r, "nanovllm"))), None)
+    if root is None:
         return None
+    try:
+        sys.path.insert(0, root)
+        mr = importlib.import_module("nanovllm.engine.model_runner")
+        refctx = importlib.import_module("nanovllm.utils.context")
+    except Exception:
+        return None
+    stub = types.SimpleNamespace(block_size=BS)
+    stub.prepare_block_tables = types.MethodType(mr.ModelRunner.prepare_block_tables, stub)
     seqs, free = make(bs, ctx)
     spent = 0.0
     n = min(steps, 300)
     for step in range(n):
         advance(seqs, free, step)
         t0 = time.perf_counter()
-        ref.mr.ModelRunner.prepare_decode(ref.stub, seqs)     # on the GPU box: real pinned tensors + .cuda() copies
+        mr.ModelRunner.prepare_decode(stub, seqs)
         spent += time.perf_counter() - t0
-        ref.ctx.reset_context()
+        refctx.reset_context()
     torch.cuda.synchronize()
     return round(spent / n * 1e6, 2)
 
