@@ -7,7 +7,9 @@
  * handle (cudaStream_t passed as void*), and returns an int status
  * (NVLLM_OK == 0).  No torch types, no exceptions, no allocation per call:
  * the caller owns every buffer including the output and the split-KV
- * workspace, so every call is CUDA-graph capturable.
+ * workspace, so every call is CUDA-graph capturable (this sentence is about
+ * the entry points that take a workspace; it says nothing about
+ * nvllm_paged_decode_noalloc, section (2b)).
  *
  * Reference interfaces replaced (paths relative to the reference repo):
  *   nvllm_store_kvcache     <- nanovllm/layers/attention.py:19-55
@@ -143,6 +145,63 @@ NVLLM_API int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride,
                        int32_t head_dim, int32_t block_size, float scale,
                        int32_t num_splits, void* workspace,
                        size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * (2b) paged GQA decode for callers that have no way to allocate device memory.
+ *      No counterpart in the reference (there torch's caching allocator hands
+ *      flash-attn its split-KV scratch); this exists for integrations that sit
+ *      below torch.
+ *
+ *   Who needs it: nvllm_paged_decode with num_splits > 1 wants a zero-filled
+ *   workspace from the caller.  A host bound to this library over plain FFI (a
+ *   C, Go or Rust serving loop, or a plugin slot that only forwards the
+ *   tensors the engine already owns) has no torch allocator to ask, and a raw
+ *   cudaMalloc is not an option for it either: by the time decode runs the
+ *   engine has sized the KV cache to take what was left of HBM
+ *   (ModelRunner.allocate_kv_cache, gpu_memory_utilization), so the request
+ *   can fail, and cudaMalloc / cudaFree synchronise the whole device, which a
+ *   per-token serving loop cannot afford.
+ *
+ *   What it does: the same computation, the same kernel and the same arguments
+ *   as nvllm_paged_decode with the split-KV grid (num_splits in 1..128), minus
+ *   the two workspace arguments.  The arrival counters and fp32 partials live
+ *   in a fixed array of NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES (2 MiB) that
+ *   is part of the library image: every GPU on which this process has loaded
+ *   the library holds those 2 MiB until the process exits, whether or not this
+ *   function is ever called.  The function itself calls no cudaMalloc,
+ *   cudaFree or any other allocating routine.
+ *
+ *   Limit: nvllm_paged_decode_workspace_bytes(bs, num_q_heads, head_dim,
+ *   num_splits) must not exceed NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES, i.e.
+ *   64 KiB + bs * num_q_heads * num_splits * 516 B <= 2 MiB (3937 partial rows;
+ *   a one-wave grid on 148 SMs needs at most 148 * 8 = 1184).  A larger
+ *   geometry returns NVLLM_ERR_WORKSPACE before anything is launched; use
+ *   fewer splits or nvllm_paged_decode with your own buffer.  num_splits <= 0
+ *   (the balanced grid) is NVLLM_ERR_BAD_ARG here.
+ *
+ *   First call on each device: with that device current, the function looks
+ *   up the device address of the array once (cudaGetSymbolAddress; this may
+ *   also make the CUDA runtime load the library's device code) and remembers
+ *   it per device.  Make that first call during start-up, outside any stream
+ *   capture.  Later calls only enqueue work on `stream`.
+ *
+ *   Sharing: all calls on one device use the one array, and it keeps whatever
+ *   the previous call left in it.  Each call therefore begins by clearing the
+ *   arrival counters it is about to use (a cudaMemsetAsync on `stream`, ahead
+ *   of the kernel); the partials need no clearing, every one read was written
+ *   by the same launch.  Two calls that can run on the GPU at the same time
+ *   (different streams, or different host threads) would trample each other's
+ *   counters and partials: order them on one stream or with events.
+ * ---------------------------------------------------------------------- */
+#define NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES (2u << 20)
+NVLLM_API int nvllm_paged_decode_noalloc(void* out, const void* q, int64_t q_row_stride,
+                       const void* k_cache, const void* v_cache,
+                       int64_t cache_block_stride, int64_t cache_token_stride,
+                       const int32_t* block_tables, int64_t table_stride,
+                       const int32_t* context_lens,
+                       int32_t bs, int32_t num_q_heads, int32_t num_kv_heads,
+                       int32_t head_dim, int32_t block_size, float scale,
+                       int32_t num_splits, void* stream);
 
 /* Bytes of workspace for the given geometry: 0 when num_splits == 1; for
  * num_splits <= 0 (balanced grid) it depends on the CTA count only. */

@@ -23,6 +23,9 @@ SIGNATURES = {
     "nvllm_paged_decode": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64,
                                    c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                    c_float, c_int32, c_void_p, c_size_t, c_void_p]),
+    "nvllm_paged_decode_noalloc": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64,
+                                           c_void_p, c_int64, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
+                                           c_float, c_int32, c_void_p]),
     "nvllm_paged_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "nvllm_paged_decode_plan": (c_int32, [c_int32, c_int32, c_int32, c_int32, c_int32]),
     "nvllm_paged_decode_set_variant": (c_int, [c_int32]),

@@ -789,3 +789,75 @@ int nvllm_paged_decode(void* out, const void* q, int64_t q_row_stride, const voi
 }
 
 }  // extern "C"
+
+// ---- nvllm_paged_decode_noalloc: the split-KV decode for callers that cannot allocate -----------------------------
+// Declaration, limits and the reasons for it: include/nvllm_attn.h (2b).  No counterpart in the reference.
+//
+// The split-KV scratch (arrival counters + fp32 partials) sits in the library image instead of a caller buffer.  On the
+// host, `g_noalloc_scratch` is only a handle of the symbol, not an address the GPU can use: handing it to a kernel would
+// fault (or, where the GPU can reach host memory, scribble over the host-side shadow).  The device address is fetched
+// with cudaGetSymbolAddress, once per device, with that device current, and kept in g_noalloc_addr.
+namespace nvllm {
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES];
+static void* g_noalloc_addr[kMaxDevices] = {};
+
+// Device address of the scratch array on the current device.  The look-up happens on the first call per device (and on
+// every call for device ordinals >= kMaxDevices, which have no cache slot).
+static cudaError_t noalloc_scratch_address(void** addr_out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const bool cached = dev >= 0 && dev < kMaxDevices;
+  if (cached && g_noalloc_addr[dev]) {
+    *addr_out = g_noalloc_addr[dev];
+    return cudaSuccess;
+  }
+  void* addr = nullptr;
+  e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);
+  if (e != cudaSuccess) return e;
+  if (!addr) return cudaErrorInvalidSymbol;
+  if (cached) g_noalloc_addr[dev] = addr;
+  *addr_out = addr;
+  return cudaSuccess;
+}
+
+}  // namespace nvllm
+
+extern "C" int nvllm_paged_decode_noalloc(void* out, const void* q, int64_t q_row_stride, const void* k_cache,
+                                          const void* v_cache, int64_t cache_block_stride, int64_t cache_token_stride,
+                                          const int32_t* block_tables, int64_t table_stride,
+                                          const int32_t* context_lens, int32_t bs, int32_t num_q_heads,
+                                          int32_t num_kv_heads, int32_t head_dim, int32_t block_size, float scale,
+                                          int32_t num_splits, void* stream) {
+  using namespace nvllm;
+  if (num_splits < 1) return NVLLM_ERR_BAD_ARG;   // the balanced grid has its own workspace layout: not offered here
+  if (bs < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0) return NVLLM_ERR_BAD_ARG;
+  if (bs == 0) return NVLLM_OK;
+  // argument errors that need no GPU are reported before the set-up below touches the CUDA runtime
+  if (!out || !q || !k_cache || !v_cache || !block_tables || !context_lens || block_size <= 0) return NVLLM_ERR_BAD_ARG;
+  if (head_dim != kHeadDim || num_q_heads % num_kv_heads != 0 || num_q_heads / num_kv_heads > 8 ||
+      block_size % 32 != 0 || num_splits > 128)
+    return NVLLM_ERR_UNSUPPORTED;
+  if (num_splits == 1)   // one split writes the output directly: no scratch, nothing to set up
+    return nvllm_paged_decode(out, q, q_row_stride, k_cache, v_cache, cache_block_stride, cache_token_stride,
+                              block_tables, table_stride, context_lens, bs, num_q_heads, num_kv_heads, head_dim,
+                              block_size, scale, 1, nullptr, 0, stream);
+  // Beyond the fixed array: refuse before touching the GPU.  (The counter area alone bounds bs * num_kv_heads at 16384;
+  // nvllm_paged_decode checks that one.)
+  const size_t need = nvllm_paged_decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits);
+  if (need > static_cast<size_t>(NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES)) return NVLLM_ERR_WORKSPACE;
+  const size_t counter_bytes = static_cast<size_t>(bs) * num_kv_heads * sizeof(int32_t);
+  if (counter_bytes > kCounterBytes) return NVLLM_ERR_UNSUPPORTED;
+
+  void* scratch = nullptr;
+  cudaError_t e = noalloc_scratch_address(&scratch);
+  if (e != cudaSuccess) return record_cuda_error(e);
+  // The array is shared by every call and keeps the last call's bytes.  Only the arrival counters have to start at
+  // zero (a launch that died half-way would leave them non-zero); partials are always written before they are read.
+  e = cudaMemsetAsync(scratch, 0, counter_bytes, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return record_cuda_error(e);
+  return nvllm_paged_decode(out, q, q_row_stride, k_cache, v_cache, cache_block_stride, cache_token_stride,
+                            block_tables, table_stride, context_lens, bs, num_q_heads, num_kv_heads, head_dim,
+                            block_size, scale, num_splits, scratch, NVLLM_PAGED_DECODE_NOALLOC_SCRATCH_BYTES, stream);
+}
