@@ -289,6 +289,21 @@ NVLLM_API int64_t nvllm_varlen_prefill_path_count(int32_t path);
  * for the current device in *code_out; 0 = no error.  Synchronises the device:
  * call it outside graph capture (tests, end of a benchmark, engine shutdown). */
 NVLLM_API int nvllm_varlen_prefill_error(uint32_t* code_out);
+/* The same word without a CUDA call: the timed-out waiter also stores its code
+ * (bit 31 set) into a mapped pinned host word, and this reads it -- cheap enough
+ * to run before every prefill launch, which is what ops.flash_attn_varlen_func
+ * does so that a timeout surfaces as an exception on the product path instead
+ * of silently spoiling every later launch.  clear != 0 and a non-zero word: also
+ * clears the device-side latch (that branch synchronises the device).  The host
+ * word is per process: with several devices in one process it does not say
+ * which device timed out, and clear re-arms the current device only.
+ * The tcgen05 tile of nvllm_rowparallel_linear_allreduce has a latch of its own;
+ * it reports through nvllm_rowparallel_poll_error. */
+NVLLM_API int nvllm_varlen_prefill_poll_error(uint32_t* error_out, int32_t clear);
+/* Test hook: enqueues a one-thread kernel that waits 1 ms on an mbarrier nobody
+ * completes, in the prefill unit (unit 0) or the RowParallelLinear unit (unit 1),
+ * so the tests can watch a timeout travel to the host and be cleared again. */
+NVLLM_API int nvllm_tc_latch_selftest(int32_t unit, void* stream);
 
 /* ------------------------------------------------------------------------
  * (3b) fused pre-attention step (SURVEY §8f "next", rank 1): per-head q/k
@@ -521,7 +536,9 @@ NVLLM_API int nvllm_tp_comm_enable_peer(int32_t peer_device);
 NVLLM_API int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* error_out);
 /* Non-blocking: the timeout latch as a mapped pinned HOST word (0 = none, else 1 + the tile whose peer never
  * arrived in some launch of this process); plain memory read, no CUDA call, usable after every launch or graph
- * replay.  clear != 0 resets it.  The results of a call that timed out are undefined. */
+ * replay.  clear != 0 resets it.  The results of a call that timed out are undefined.
+ * When no peer timeout is pending it reports the mbarrier-timeout latch of the kernel's tcgen05 tile instead (bit 31
+ * set; see nvllm_varlen_prefill_poll_error); clearing that one also re-arms the device-side latch (synchronises). */
 NVLLM_API int nvllm_rowparallel_poll_error(uint32_t* error_out, int32_t clear);
 NVLLM_API int nvllm_rowparallel_linear_allreduce(void* y, int64_t y_row_stride,
                                        const void* x, int64_t x_row_stride,

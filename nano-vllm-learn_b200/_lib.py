@@ -39,6 +39,8 @@ SIGNATURES = {
     "nvllm_varlen_prefill_last_path": (c_int32, []),
     "nvllm_varlen_prefill_path_count": (c_int64, [c_int32]),
     "nvllm_varlen_prefill_error": (c_int, [ctypes.POINTER(ctypes.c_uint32)]),
+    "nvllm_varlen_prefill_poll_error": (c_int, [ctypes.POINTER(ctypes.c_uint32), c_int32]),
+    "nvllm_tc_latch_selftest": (c_int, [c_int32, c_void_p]),
     "nvllm_qk_norm_rope_store": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
                                          c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
                                          c_int32, c_int32, c_void_p]),

@@ -34,5 +34,8 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
 
 // returns (and clears) the tcgen05 kernel's mbarrier-timeout latch on the current device; synchronises
 int prefill_tcgen05_error_fetch(unsigned int* code);
+unsigned int prefill_tcgen05_error_poll();                 // mapped host word: no CUDA call
+int prefill_tcgen05_latch_selftest(cudaStream_t stream);   // test hook: a wait that times out after 1 ms
+int rp_tc_latch_selftest(cudaStream_t stream);             // the same in rowparallel_allreduce.cu's unit
 
 }  // namespace nvllm

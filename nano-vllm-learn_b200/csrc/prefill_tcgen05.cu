@@ -478,6 +478,9 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
   cudaError_t e0 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
 #endif
   if (e0 != cudaSuccess) return record_cuda_error(e0);
+  // timeout latch -> mapped host word, once per device (prefill launches are eager: the reference captures decode only);
+  // a refusal keeps the device-only latch
+  if (tc::tc_error_arm() != cudaSuccess) cudaGetLastError();
   const int num_pairs = pp.pair_heads ? (max_seqlen_q + TM - 1) / TM : (max_seqlen_q + 2 * TM - 1) / (2 * TM);
   const int64_t total = static_cast<int64_t>(num_pairs) * (pp.pair_heads ? pp.num_q_heads / 2 : pp.num_q_heads) * batch;
   if (total > INT32_MAX) return NVLLM_ERR_UNSUPPORTED;
@@ -490,6 +493,8 @@ int launch_prefill_tcgen05(const PrefillParams& p, int batch, int max_seqlen_q, 
 }
 
 int prefill_tcgen05_error_fetch(unsigned int* code) { return record_cuda_error(tc::tc_error_fetch(code)); }
+unsigned int prefill_tcgen05_error_poll() { return tc::tc_error_poll(); }
+int prefill_tcgen05_latch_selftest(cudaStream_t stream) { return record_cuda_error(tc::tc_latch_selftest(stream)); }
 
 }  // namespace nvllm
 

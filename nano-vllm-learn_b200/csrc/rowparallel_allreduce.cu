@@ -636,6 +636,8 @@ cudaError_t rp_warm_device() {
     if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, rp_kernel(128, 64, 8));
     if (e != cudaSuccess) return e;
   }
+  // mbarrier-timeout latch of the tcgen05 tile -> mapped host word (tcgen05.cuh); a refusal keeps the device-only latch
+  if (tc::tc_error_arm() != cudaSuccess) cudaGetLastError();
   if (dev < 64) done[dev] = true;
   return cudaSuccess;
 }
@@ -762,6 +764,9 @@ int rp_plan(int n_tokens, int k_per_rank, int out_features, int world, RpPlan* p
 }
 
 }  // namespace
+
+// test hook (nvllm_tc_latch_selftest, unit 1): a wait in THIS unit that times out after 1 ms
+int rp_tc_latch_selftest(cudaStream_t stream) { return record_cuda_error(tc::tc_latch_selftest(stream)); }
 }  // namespace nvllm
 
 using namespace nvllm;
@@ -887,8 +892,15 @@ int nvllm_tp_comm_status(const void* dev_ptr, uint32_t* epoch_out, uint32_t* err
 int nvllm_rowparallel_poll_error(uint32_t* error_out, int32_t clear) {
   if (!error_out) return NVLLM_ERR_BAD_ARG;
   uint32_t* w = rp_host_error_word();
-  *error_out = w ? *reinterpret_cast<volatile uint32_t*>(w) : 0u;
+  const uint32_t peer = w ? *reinterpret_cast<volatile uint32_t*>(w) : 0u;
+  // the tcgen05 tile's mbarrier-timeout latch (bit 31 set) reports through the same call: both are host memory reads
+  const uint32_t tile = tc::tc_error_poll();
+  *error_out = peer ? peer : tile;
   if (w && clear) *reinterpret_cast<volatile uint32_t*>(w) = 0u;
+  if (tile && clear) {   // error path only: re-arms the device-side latch too (synchronises the current device)
+    unsigned int v = 0;
+    return record_cuda_error(tc::tc_error_fetch(&v));
+  }
   return NVLLM_OK;
 }
 

@@ -39,19 +39,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded spin: a protocol bug must neither hang the GPU box nor kill the CUDA context.  After kMbarTimeoutNs
-// the waiter latches an error word (one per translation unit, read and cleared by the host through
-// tc_error_fetch) and returns as if the barrier had completed; every other wait of the grid sees the latch at
-// its next check and returns too, so the launch drains quickly with undefined results and the HOST reports the
-// failure (nvllm_varlen_prefill_error) instead of a device trap poisoning the process.
+// Bounded spin: a protocol bug must neither hang the GPU box nor kill the CUDA context.  After the timeout the
+// waiter latches an error word and returns as if the barrier had completed; every other wait of the grid sees the
+// latch at its next check and returns too, so the launch drains quickly with undefined results.  The latch is one
+// per translation unit (prefill, RowParallelLinear tile).  The waiter also stores the code into a mapped, pinned
+// HOST word of the same unit (tc_error_arm), so the product path notices at its next launch with one plain memory
+// read (tc_error_poll) -- no CUDA call, no synchronisation -- raises, and clears both words (tc_error_fetch): a
+// timeout spoils the launches already queued behind it, never the ones after the host's next call.
 static __device__ unsigned int g_tc_error_latch = 0;
+static __device__ unsigned int* g_tc_error_host = nullptr;     // device view of the unit's host word (null until armed)
 constexpr unsigned long long kMbarTimeoutNs = 2000000000ull;   // 2 s; a legitimate wait is microseconds
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
   return t;
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity, unsigned long long timeout_ns) {
   uint32_t spins = 0;
   unsigned long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
@@ -60,23 +63,92 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (*reinterpret_cast<volatile unsigned int*>(&g_tc_error_latch) != 0u) return;
     const unsigned long long now = global_timer_ns();
     if (t0 == 0) t0 = now;
-    if (now - t0 > kMbarTimeoutNs) {
-      atomicCAS(&g_tc_error_latch, 0u, 0x80000000u | (bar & 0xFFFFu) | ((parity & 1u) << 16));
+    if (now - t0 > timeout_ns) {
+      const unsigned int code = 0x80000000u | (bar & 0xFFFFu) | ((parity & 1u) << 16);
+      if (atomicCAS(&g_tc_error_latch, 0u, code) == 0u) {
+        unsigned int* host = *reinterpret_cast<unsigned int* volatile*>(&g_tc_error_host);
+        if (host) {
+          *reinterpret_cast<volatile unsigned int*>(host) = code;
+          __threadfence_system();
+        }
+      }
       return;
     }
   }
 }
-// Host side: returns and clears the latch of THIS translation unit on the current device (synchronises).
-inline cudaError_t tc_error_fetch(unsigned int* out) {
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) { mbar_wait_bounded(bar, parity, kMbarTimeoutNs); }
+
+// ---- host side of the latch.  `static`: every translation unit that includes this header owns its own copy of the
+// functions, bound to its own g_tc_error_latch / g_tc_error_host.
+// The unit's host word: 64 bytes of mapped pinned memory, allocated at first use, never freed.  nullptr if refused.
+static inline unsigned int* tc_error_host_word() {
+  static unsigned int* word = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      for (int i = 0; i < 16; ++i) static_cast<volatile unsigned int*>(p)[i] = 0u;
+      word = static_cast<unsigned int*>(p);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return word;
+}
+// Points the CURRENT device's g_tc_error_host at the host word; once per device (cudaMemcpyToSymbol: call it from
+// set-up code or an eager launch, not while a stream is being captured).  A refusal leaves the device-only latch.
+static inline cudaError_t tc_error_arm() {
+  static bool armed[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && armed[dev]) return cudaSuccess;
+  unsigned int* hw = tc_error_host_word();
+  if (hw) {
+    void* dp = nullptr;
+    e = cudaHostGetDevicePointer(&dp, hw, 0);
+    if (e != cudaSuccess) return e;
+    unsigned int* dpw = static_cast<unsigned int*>(dp);
+    e = cudaMemcpyToSymbol(g_tc_error_host, &dpw, sizeof(dpw));
+    if (e != cudaSuccess) return e;
+  }
+  if (dev >= 0 && dev < 64) armed[dev] = true;
+  return cudaSuccess;
+}
+// One host memory read: the code of a timeout seen by any launch of this unit since the last fetch, 0 = none.
+static inline unsigned int tc_error_poll() {
+  unsigned int* hw = tc_error_host_word();
+  return hw ? *reinterpret_cast<volatile unsigned int*>(hw) : 0u;
+}
+// Returns and clears the latch of THIS translation unit on the current device, and the host word (synchronises).
+static inline cudaError_t tc_error_fetch(unsigned int* out) {
   unsigned int v = 0;
   cudaError_t e = cudaMemcpyFromSymbol(&v, g_tc_error_latch, sizeof(v));
   if (e != cudaSuccess) return e;
-  *out = v;
+  unsigned int* hw = tc_error_host_word();
+  const unsigned int hv = hw ? *reinterpret_cast<volatile unsigned int*>(hw) : 0u;
+  *out = v ? v : hv;
   if (v != 0u) {
     const unsigned int zero = 0u;
     e = cudaMemcpyToSymbol(g_tc_error_latch, &zero, sizeof(zero));
   }
+  if (hw && hv != 0u) *reinterpret_cast<volatile unsigned int*>(hw) = 0u;
   return e;
+}
+// Self-test of the latch plumbing: one thread waits 1 ms on a barrier nobody completes.
+static __global__ void tc_latch_selftest_kernel() {
+  __shared__ __align__(8) unsigned long long bar;
+  const uint32_t b = static_cast<uint32_t>(__cvta_generic_to_shared(&bar));
+  mbar_init(b, 1);
+  fence_barrier_init();
+  mbar_wait_bounded(b, 0, 1000000ull);
+}
+static inline cudaError_t tc_latch_selftest(cudaStream_t stream) {
+  cudaError_t e = tc_error_arm();
+  if (e != cudaSuccess) return e;
+  tc_latch_selftest_kernel<<<1, 1, 0, stream>>>();
+  return cudaGetLastError();
 }
 
 // One lane of a fully converged warp.  The TMA / MMA roles run warp-wide (uniform control flow, so descriptors

@@ -261,6 +261,22 @@ int nvllm_varlen_prefill_error(uint32_t* code_out) {
   return rc;
 }
 
+int nvllm_varlen_prefill_poll_error(uint32_t* error_out, int32_t clear) {
+  if (!error_out) return NVLLM_ERR_BAD_ARG;
+  *error_out = nvllm::prefill_tcgen05_error_poll();
+  if (*error_out && clear) {   // error path only: clears the device-side latch as well (synchronises)
+    unsigned int v = 0;
+    return nvllm::prefill_tcgen05_error_fetch(&v);
+  }
+  return NVLLM_OK;
+}
+
+int nvllm_tc_latch_selftest(int32_t unit, void* stream) {
+  if (unit == 0) return nvllm::prefill_tcgen05_latch_selftest(static_cast<cudaStream_t>(stream));
+  if (unit == 1) return nvllm::rp_tc_latch_selftest(static_cast<cudaStream_t>(stream));
+  return NVLLM_ERR_BAD_ARG;
+}
+
 int nvllm_varlen_prefill_set_variant(int32_t variant) {
   if (variant < -1 || variant > 1) return NVLLM_ERR_BAD_ARG;
   nvllm::g_prefill_variant = variant;

@@ -77,6 +77,27 @@ def prefill_error() -> int:
     return int(code.value)
 
 
+def prefill_poll_error(clear: bool = False) -> int:
+    """The same latch through its mapped host word: one ctypes call and one host memory read, no CUDA call (0 = none).
+    clear=True with a pending error also clears the device-side latch (that path synchronises)."""
+    import ctypes
+    code = ctypes.c_uint32(0)
+    _lib.check(_lib.load().nvllm_varlen_prefill_poll_error(ctypes.byref(code), 1 if clear else 0),
+               "varlen_prefill_poll_error")
+    return int(code.value)
+
+
+def raise_on_prefill_timeout() -> None:
+    """Product-path check: flash_attn_varlen_func calls this before every eager launch, so an mbarrier
+    timeout of an EARLIER tcgen05 prefill launch becomes an exception at the next call instead of a sticky latch that
+    lets every later wait return early.  The latch is cleared before raising: launches after the exception are clean."""
+    code = prefill_poll_error()
+    if code:
+        prefill_poll_error(clear=True)
+        raise _lib.NvllmError(f"tcgen05 prefill: an mbarrier wait timed out (code {code:#x}); the outputs of the prefill "
+                              f"launches queued since are undefined.  The latch has been cleared")
+
+
 def set_decode_variant(variant: int) -> None:
     _lib.check(_lib.load().nvllm_paged_decode_set_variant(variant), "set_decode_variant")
 
@@ -230,6 +251,8 @@ def flash_attn_varlen_func(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, ma
         out = torch.empty((total_q, num_q_heads, head_dim), dtype=q.dtype, device=q.device)
     if total_q == 0 or batch <= 0:
         return out
+    if not torch.cuda.is_current_stream_capturing():
+        raise_on_prefill_timeout()
     if block_table is not None:
         assert k.dim() == 4 and v.shape == k.shape and v.stride() == k.stride()
         assert block_table.dtype == torch.int32 and block_table.stride(-1) == 1 and block_table.size(0) == batch

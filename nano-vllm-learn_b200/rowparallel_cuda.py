@@ -161,6 +161,10 @@ def raise_on_timeout() -> None:
     """Turn a latched peer timeout into an exception, as NCCL would: called after every eager fused
     forward and after every graph replay by the runner glue.  Costs one ctypes call and one host memory read."""
     err = poll_error()
+    if err & 0x80000000:    # the tcgen05 tile's mbarrier-timeout latch (csrc/tcgen05.cuh), not a peer timeout
+        poll_error(clear=True)
+        raise _lib.NvllmError(f"fused RowParallelLinear tcgen05 tile: an mbarrier wait timed out (code {err:#x}); results "
+                              f"of the launches queued since are undefined.  The latch has been cleared")
     if err:
         poll_error(clear=True)
         raise _lib.NvllmError(f"fused RowParallelLinear all-reduce: a tensor-parallel peer never arrived (tile {err - 1}); "

@@ -110,3 +110,53 @@ def test_default_variant_is_tcgen05_and_no_timeout_latched(lib):
     assert _ops.PREFILL_KERNEL_NAMES[_ops.prefill_last_path()] == "prefill_tcgen05_kernel"
     torch.cuda.synchronize()
     assert _ops.prefill_error() == 0
+
+
+def test_mbarrier_timeout_surfaces_on_the_product_path_and_does_not_poison_later_launches(ops, lib):
+    """a timed-out mbarrier wait used to set a sticky latch nobody on the engine path read, after which
+    every later wait of the unit returned early.  Now the waiter also writes a mapped host word; the next
+    flash_attn_varlen_func call reads it, clears both words and raises; the call after that is clean."""
+    import ctypes
+    from nano_vllm_learn_b200 import _lib
+    c = cases.make_prefill_case("p_small")
+    want = orc.varlen_prefill_ref(c["q"], c["k"], c["v"], c["cu_seqlens_q"], c["cu_seqlens_k"], c["scale"])
+    g = _cuda(c)
+
+    def run():
+        return ops.flash_attn_varlen_func(g["q"], g["k"], g["v"], c["max_seqlen_q"], g["cu_seqlens_q"],
+                                          c["max_seqlen_k"], g["cu_seqlens_k"], softmax_scale=c["scale"], causal=True)
+    assert _maxerr(run(), want) <= TOL                 # also arms the host word on this device
+    assert ops.prefill_poll_error() == 0
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert lib.nvllm_tc_latch_selftest(7, stream) == 1
+    assert lib.nvllm_tc_latch_selftest(0, stream) == 0  # a 1 ms wait on a barrier nobody completes, in the prefill unit
+    torch.cuda.synchronize()
+    code = ops.prefill_poll_error()
+    assert code & 0x80000000, hex(code)
+    with pytest.raises(_lib.NvllmError, match="mbarrier wait timed out"):
+        run()
+    assert ops.prefill_poll_error() == 0               # cleared by the raise: host word ...
+    assert _maxerr(run(), want) <= TOL                 # ... and device latch: this launch waits for real again
+    assert ops.prefill_last_path() == 1
+    torch.cuda.synchronize()
+    assert ops.prefill_error() == 0
+
+
+def test_rowparallel_tile_latch_reports_through_poll_error(lib):
+    """The RowParallelLinear unit has its own copy of the latch; it reports through nvllm_rowparallel_poll_error."""
+    import ctypes
+    from nano_vllm_learn_b200 import _lib, rowparallel_cuda as rp
+    assert rp.poll_error() == 0
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert lib.nvllm_tc_latch_selftest(1, stream) == 0
+    torch.cuda.synchronize()
+    assert rp.poll_error() & 0x80000000
+    from nano_vllm_learn_b200 import ops as _ops
+    assert _ops.prefill_poll_error() == 0               # the prefill unit's latch is a different word
+    with pytest.raises(_lib.NvllmError, match="tcgen05 tile"):
+        rp.raise_on_timeout()
+    assert rp.poll_error() == 0
+    assert lib.nvllm_tc_latch_selftest(1, stream) == 0  # the device latch was cleared too: a second timeout latches again
+    torch.cuda.synchronize()
+    assert rp.poll_error() & 0x80000000
+    assert rp.poll_error(clear=True) & 0x80000000 and rp.poll_error() == 0
