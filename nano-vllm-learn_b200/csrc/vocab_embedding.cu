@@ -81,7 +81,12 @@ __global__ void __launch_bounds__(kEmbThreads) vocab_embedding_kernel(const EmbP
   const int64_t id = p.ids[t];
   const int64_t local = id - p.vocab_start;
   __nv_bfloat16* yrow = p.y + static_cast<int64_t>(t) * p.y_stride;
-  if (local >= 0 && local < p.vocab_per_rank) {
+  if (id < 0 || id >= static_cast<int64_t>(p.world) * p.vocab_per_rank) {
+    // no rank owns this id, so nobody would ever send its row: every rank sees the same id and writes the zeros the
+    // reference produces (all masks false -> all_reduce of zero rows, embed_head.py:35-43) without waiting (ADVICE r2:
+    // this used to spin for the whole timeout, at every replay of a captured graph)
+    for (int u = tid; u < units; u += kEmbThreads) *reinterpret_cast<uint2*>(yrow + 4 * u) = make_uint2(0u, 0u);
+  } else if (local >= 0 && local < p.vocab_per_rank) {
     // owner: before overwriting the parity used by call epoch-2, every peer must have entered call epoch-1
     __shared__ int ok;
     if (tid == 0) {

@@ -88,6 +88,31 @@ def test_many_calls_without_host_sync_and_a_rank_that_owns_everything(lib, sprea
     assert all(cm.status() == (40, 0) for cm in comms)
 
 
+def test_ids_no_rank_owns_give_zero_rows_at_once(lib):
+    """an id outside [0, world * vocab_per_rank) has no owner; every rank used to wait the full 20 s timeout
+    for a row nobody sends.  The reference answers zeros (no mask matches, embed_head.py:35-43) and so does the kernel,
+    without any wait and without latching an error; owned ids in the same call are unaffected."""
+    import time
+    from nano_vllm_learn_b200 import embedding_cuda
+    world, vocab, hidden = 2, 1024, 256
+    g = torch.Generator().manual_seed(23)
+    weight = torch.randn(vocab, hidden, generator=g).to(torch.bfloat16)
+    comms, shards, streams = _world([0, 0], weight, hidden)
+    x = torch.tensor([5, vocab, 700, -1, vocab + 12345, 0, vocab - 1], dtype=torch.int64)
+    want = torch.zeros(len(x), hidden, dtype=torch.bfloat16)
+    owned = (x >= 0) & (x < vocab)
+    want[owned] = weight[x[owned]]
+    torch.cuda.synchronize()
+    t0 = time.time()
+    for _ in range(3):
+        outs = _call([0, 0], comms, shards, streams, x)
+    torch.cuda.synchronize()
+    assert time.time() - t0 < 5.0
+    for r, y in enumerate(outs):
+        assert torch.equal(y.cpu().view(torch.int16), want.view(torch.int16)), f"rank {r}"
+    assert embedding_cuda.poll_error() == 0 and all(cm.status() == (3, 0) for cm in comms)
+
+
 def test_graph_replay_loopback(lib):
     """The decode graph captures the embedding: the call epoch lives on the device, so replays need no host help."""
     from nano_vllm_learn_b200 import ops
