@@ -10,6 +10,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 
 from . import _lib
@@ -165,7 +167,8 @@ def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: tor
 
 def plan_num_splits(bs: int, num_q_heads: int, num_kv_heads: int, max_ctx: int) -> int:
     """Split count (>= 1) of the split-KV decode grid; 0 (balanced persistent grid) only under NVLLM_DECODE_PLAN=balanced."""
-    key = (bs, num_q_heads, num_kv_heads, max_ctx)
+    # the plan depends on NVLLM_DECODE_PLAN, which the C side reads per call: the cached answer must too (ADVICE r2)
+    key = (bs, num_q_heads, num_kv_heads, max_ctx, os.environ.get("NVLLM_DECODE_PLAN"))
     s = _PLAN_CACHE.get(key)
     if s is None:
         s = int(_lib.load().nvllm_paged_decode_plan(bs, num_q_heads, num_kv_heads, max_ctx, 0))
@@ -181,12 +184,14 @@ def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: tor
                             cache_seqlens: torch.Tensor, block_table: torch.Tensor,
                             softmax_scale: Optional[float] = None, causal: bool = True,
                             num_splits: Optional[int] = None, out: Optional[torch.Tensor] = None,
-                            workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+                            workspace: Optional[torch.Tensor] = None,
+                            balanced_ctas: Optional[int] = None) -> torch.Tensor:
     """Paged decode.  q [bs, 1, Hq, D] (or [bs, Hq, D]); returns the same shape.
 
     `causal` is accepted for signature parity; with one query token the bottom-right causal mask is
-    a no-op.  num_splits=None lets the library plan from (bs, Hkv, table width) only; >= 1 is the split-KV grid,
-    0 (or -P) the opt-in balanced persistent grid with one CTA per SM (or P CTAs).
+    a no-op.  num_splits=None or 0 ("choose automatically", as in flash-attn's signature) lets the library plan from
+    (bs, Hkv, table width) only; >= 1 is the split-KV grid with that many splits.  The opt-in balanced persistent grid
+    (slower on every measured shape) is selected by `balanced_ctas` alone: 0 = fill the SMs, P > 0 = P CTAs.
     """
     lib = _lib.load()
     _require_cuda(q, k_cache, v_cache, cache_seqlens, block_table)
@@ -206,8 +211,13 @@ def flash_attn_with_kvcache(q: torch.Tensor, k_cache: torch.Tensor, v_cache: tor
     assert block_table.dtype == torch.int32 and block_table.stride(-1) == 1 and block_table.size(0) == bs
     if softmax_scale is None:
         softmax_scale = head_dim ** -0.5
-    if num_splits is None:
+    if balanced_ctas is not None:
+        assert balanced_ctas >= 0 and not num_splits, "balanced_ctas excludes an explicit split count"
+        num_splits = -int(balanced_ctas)       # the C ABI's encoding (include/nvllm_attn.h): <= 0 is the balanced grid
+    elif not num_splits:
         num_splits = plan_num_splits(bs, num_q_heads, num_kv_heads, block_table.size(1) * block_size)
+    elif num_splits < 0:
+        raise ValueError("num_splits must be None/0 (automatic) or >= 1; the balanced grid is balanced_ctas=")
     if out is None:
         out = torch.empty((bs, num_q_heads, head_dim), dtype=q.dtype, device=q.device)
     ws_bytes = decode_workspace_bytes(bs, num_q_heads, head_dim, num_splits)

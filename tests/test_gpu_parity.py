@@ -130,10 +130,38 @@ def test_decode_balanced_vs_oracle_and_fixture(ops, min_chunks, name, ctas, mc, 
     min_chunks(mc, warps)
     for _ in range(2):   # twice: the arrival counters of the shared workspace must have reset themselves
         got = ops.flash_attn_with_kvcache(g["q"].unsqueeze(1), g["k_cache"], g["v_cache"], g["context_lens"],
-                                          g["block_tables"], softmax_scale=c["scale"], num_splits=ctas)
+                                          g["block_tables"], softmax_scale=c["scale"], balanced_ctas=-ctas)
         assert _maxerr(got.squeeze(1), want) <= TOL
     gold = cases.from_bits(np.load(os.path.join(GOLD, f"decode_{name}.npz"))["out"])
     assert _maxerr(got.squeeze(1), gold) <= TOL   # the reference's own sdpa.math output
+
+
+def test_num_splits_zero_means_automatic_like_flash_attn(ops, lib, monkeypatch):
+    """flash-attn's `num_splits=0` is 'choose for me'; it must not select the (slower) balanced grid, which
+    has its own keyword.  The plan cache follows NVLLM_DECODE_PLAN."""
+    monkeypatch.delenv("NVLLM_DECODE_PLAN", raising=False)
+    c = cases.make_decode_case("ragged_g4")
+    g = _cuda(c)
+    args = (g["q"], g["k_cache"], g["v_cache"], g["context_lens"], g["block_tables"])
+    auto = ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"])
+    n = lib.nvllm_launch_count()
+    zero = ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"], num_splits=0)
+    assert lib.nvllm_launch_count() == n + 1 and torch.equal(zero, auto)
+    planned = ops.plan_num_splits(len(c["context_lens"]), c["hq"], c["hkv"], g["block_tables"].size(1) * 256)
+    assert planned >= 1
+    assert torch.equal(ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"], num_splits=planned), auto)
+    with pytest.raises(ValueError):
+        ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"], num_splits=-3)
+    with pytest.raises(AssertionError):
+        ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"], num_splits=2, balanced_ctas=0)
+    bal = ops.flash_attn_with_kvcache(*args, softmax_scale=c["scale"], balanced_ctas=0)
+    assert _maxerr(bal, auto) <= 4e-3
+    # the cached plan follows the environment without clearing the cache by hand
+    assert ops.plan_num_splits(64, 16, 8, 4096) == 1
+    monkeypatch.setenv("NVLLM_DECODE_PLAN", "balanced")
+    assert ops.plan_num_splits(64, 16, 8, 4096) == 0
+    monkeypatch.delenv("NVLLM_DECODE_PLAN")
+    assert ops.plan_num_splits(64, 16, 8, 4096) == 1
 
 
 def test_decode_default_plan_is_the_fixed_grid(ops, monkeypatch):
@@ -212,10 +240,11 @@ def test_decode_edges(ops, min_chunks):
     tables = g["block_tables"].clone()
     tables[tables < 0] = 0
     for splits in (1, 4, 0, -5):
+        kw = dict(num_splits=splits) if splits >= 1 else dict(balanced_ctas=-splits)   # <= 0: the balanced grid
         got = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], lens, tables,
-                                          softmax_scale=c["scale"], num_splits=splits)
+                                          softmax_scale=c["scale"], **kw)
         ref = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], g["context_lens"], g["block_tables"],
-                                          softmax_scale=c["scale"], num_splits=splits)
+                                          softmax_scale=c["scale"], **kw)
         assert torch.count_nonzero(got[1]) == 0
         if splits >= 1:    # the fixed grid gives every (sequence, kv head) its own CTAs: other rows keep their bits
             assert torch.equal(got[0], ref[0]) and torch.equal(got[2:], ref[2:])
@@ -223,7 +252,7 @@ def test_decode_edges(ops, min_chunks):
             assert _maxerr(got[0], ref[0]) <= 4e-3 and _maxerr(got[2:], ref[2:]) <= 4e-3
     # every row empty (a fully padded captured batch): zeros from the balanced grid too
     got = ops.flash_attn_with_kvcache(g["q"], g["k_cache"], g["v_cache"], torch.zeros_like(lens), tables,
-                                      softmax_scale=c["scale"], num_splits=0)
+                                      softmax_scale=c["scale"], balanced_ctas=0)
     assert torch.count_nonzero(got) == 0
     # bs == 0
     empty = ops.flash_attn_with_kvcache(g["q"][:0], g["k_cache"], g["v_cache"], lens[:0], tables[:0],
@@ -265,12 +294,13 @@ def test_decode_full_size_properties(ops):
     scale = 128 ** -0.5
     o1 = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=1)
     # (i) split invariance (planned splits and an odd count)
-    for s in (None, 0, -37, 2, 5):
-        os_ = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=s)
-        assert _maxerr(os_, o1) <= 4e-3
+    for kw in (dict(num_splits=None), dict(num_splits=0), dict(balanced_ctas=0), dict(balanced_ctas=37),
+               dict(num_splits=2), dict(num_splits=5)):
+        os_ = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, **kw)
+        assert _maxerr(os_, o1) <= 4e-3, kw
     # the balanced grid is deterministic and page-placement invariant as well
-    ob = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=0)
-    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, num_splits=0))
+    ob = ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, balanced_ctas=0)
+    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc, vc, lens, tables, softmax_scale=scale, balanced_ctas=0))
     # (ii) page-permutation invariance: move every page elsewhere, remap the table -> identical bits
     nblk = kc.shape[0]
     perm = torch.randperm(nblk, device=DEV)
@@ -282,7 +312,7 @@ def test_decode_full_size_properties(ops):
     t2[live] = inv[tables[live].long()].to(torch.int32)
     o2 = ops.flash_attn_with_kvcache(q, kc2, vc2, lens, t2, softmax_scale=scale, num_splits=1)
     assert torch.equal(o1, o2)
-    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc2, vc2, lens, t2, softmax_scale=scale, num_splits=0))
+    assert torch.equal(ob, ops.flash_attn_with_kvcache(q, kc2, vc2, lens, t2, softmax_scale=scale, balanced_ctas=0))
     # (iii) linearity in V (K fixed -> identical softmax weights): out(V) + out(V') == out(V + V') up to bf16 rounding
     vb = torch.randn_like(vc)
     oa = ops.flash_attn_with_kvcache(q, kc, vb, lens, tables, softmax_scale=scale, num_splits=1)
@@ -308,7 +338,7 @@ def test_decode_balanced_ragged_batch(ops):
     scale = 128 ** -0.5
     ref = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, num_splits=1)
     for ctas in (0, -148, -61, -9):
-        got = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, num_splits=ctas)
+        got = ops.flash_attn_with_kvcache(q, kc, vc, lens, wide, softmax_scale=scale, balanced_ctas=-ctas)
         assert _maxerr(got, ref) <= 4e-3, ctas
         assert torch.count_nonzero(got[lens == 0]) == 0
     for b in (1, 8, 19, 48):

@@ -143,7 +143,7 @@ def main():
             lib.nvllm_paged_decode_set_tuning(mc, warps)
             ws = torch.zeros(max(ops.decode_workspace_bytes(bs, hq, D, min(ctas, 0)), 16), dtype=torch.uint8, device=dev)
             f = lambda i: ops.flash_attn_with_kvcache(sets[i % ncopy][0], sets[i % ncopy][1], sets[i % ncopy][2], lens,
-                                                      sets[i % ncopy][4], softmax_scale=D ** -0.5, num_splits=min(ctas, 0),
+                                                      sets[i % ncopy][4], softmax_scale=D ** -0.5, balanced_ctas=max(-ctas, 0),
                                                       out=out, workspace=ws)
             med, mn = timeit(f, flush)
             gmed, gmn = timeit_graph(f, ncopy)
