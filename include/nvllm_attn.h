@@ -392,6 +392,11 @@ NVLLM_API int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions,
                                int32_t n_patch, int32_t pad_col_begin,
                                int32_t pad_col_end, void* stream);
 NVLLM_API int32_t nvllm_advance_decode_state_max_patches(void);
+/* A row whose new token lands in a table column without a block (negative entry: a patch was not delivered) is
+ * parked by the kernel -- slot -1, context length 0, so nothing is stored and no page is read for it -- and 1 + the row
+ * index is written to a mapped pinned host word.  This reads that word (plain memory read, no CUDA call; 0 = none);
+ * clear != 0 resets it.  RunnerGlue polls it at every decode step and raises. */
+NVLLM_API int nvllm_advance_decode_state_poll_error(uint32_t* error_out, int32_t clear);
 
 /* ------------------------------------------------------------------------
  * (5) fused token sampler (SURVEY §8f "next", rank 4): one launch for the

@@ -73,6 +73,7 @@ SIGNATURES = {
     "nvllm_advance_decode_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int32,
                                            c_int32, _P32, _P32, _P32, c_int32, c_int32, c_int32, c_void_p]),
     "nvllm_advance_decode_state_max_patches": (c_int32, []),
+    "nvllm_advance_decode_state_poll_error": (c_int, [ctypes.POINTER(ctypes.c_uint32), c_int32]),
     "nvllm_vocab_embedding_comm_bytes": (c_size_t, [c_int32, c_int32, c_int32]),
     "nvllm_vocab_parallel_embedding": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32,
                                                c_int32, c_int32, ctypes.POINTER(c_void_p), c_size_t, c_int32, c_int32,

@@ -31,7 +31,28 @@ struct AdvanceParams {
   int32_t bs, block_size, n_patch;
   int32_t pad_col_begin, pad_col_end;   // table columns that join the live width this step: -1 like the reference's padding
   int32_t patch_row[kMaxPatches], patch_col[kMaxPatches], patch_val[kMaxPatches];
+  uint32_t* host_error;                 // mapped pinned host word (may be null): 1 + row whose table entry was missing
 };
+
+// A row whose new token falls into a table column that holds no block (-1 padding: the host forgot a patch) must not
+// turn into a negative slot and an out-of-range page read.  The row is parked instead -- slot -1 (store_kvcache
+// skips it), context length 0 (the decode kernel writes zeros and reads nothing) -- and the mapped host word tells
+// the glue, which raises at its next step (nvllm_advance_decode_state_poll_error: one host memory read).
+uint32_t* advance_host_error_word() {
+  static uint32_t* word = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, 64, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      for (int i = 0; i < 16; ++i) static_cast<volatile uint32_t*>(q)[i] = 0u;
+      word = static_cast<uint32_t*>(q);
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return word;
+}
 
 __global__ void __launch_bounds__(128) advance_decode_state_kernel(const AdvanceParams p) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -47,6 +68,15 @@ __global__ void __launch_bounds__(128) advance_decode_state_kernel(const Advance
   const int32_t blk = row[last / p.block_size];
   p.input_ids[b] = p.sampled[b];
   p.positions[b] = static_cast<int64_t>(len);   // the reference feeds len(seq), model_runner.py:251
+  if (blk < 0) {                                // no block behind the new token: park the row and tell the host
+    p.context_lens[b] = 0;
+    p.slot_mapping[b] = -1;
+    if (p.host_error) {
+      *reinterpret_cast<volatile uint32_t*>(p.host_error) = 1u + static_cast<uint32_t>(b);
+      __threadfence_system();
+    }
+    return;
+  }
   p.context_lens[b] = len;
   p.slot_mapping[b] = blk * p.block_size + last % p.block_size;
 }
@@ -55,6 +85,14 @@ __global__ void __launch_bounds__(128) advance_decode_state_kernel(const Advance
 }  // namespace nvllm
 
 extern "C" int32_t nvllm_advance_decode_state_max_patches(void) { return nvllm::kMaxPatches; }
+
+extern "C" int nvllm_advance_decode_state_poll_error(uint32_t* error_out, int32_t clear) {
+  if (!error_out) return NVLLM_ERR_BAD_ARG;
+  uint32_t* w = nvllm::advance_host_error_word();
+  *error_out = w ? *reinterpret_cast<volatile uint32_t*>(w) : 0u;
+  if (w && clear) *reinterpret_cast<volatile uint32_t*>(w) = 0u;
+  return NVLLM_OK;
+}
 
 extern "C" int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions, int32_t* slot_mapping,
                                           int32_t* context_lens, int32_t* block_tables, int64_t table_row_stride,
@@ -89,6 +127,12 @@ extern "C" int nvllm_advance_decode_state(int64_t* input_ids, int64_t* positions
     p.patch_row[i] = patch_rows[i];
     p.patch_col[i] = patch_cols[i];
     p.patch_val[i] = patch_vals[i];
+  }
+  p.host_error = nullptr;
+  if (uint32_t* hw = advance_host_error_word()) {
+    void* dp = nullptr;
+    if (cudaHostGetDevicePointer(&dp, hw, 0) == cudaSuccess) p.host_error = static_cast<uint32_t*>(dp);
+    else cudaGetLastError();
   }
   advance_decode_state_kernel<<<(bs + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(p);
   note_launch();

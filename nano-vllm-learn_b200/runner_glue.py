@@ -99,6 +99,7 @@ class RunnerGlue:
         self._max_patches = int(self.lib.nvllm_advance_decode_state_max_patches())
         self._patch = np.zeros((3, self._max_patches), dtype=np.int32)
         self._patch_ptrs = tuple(_i32ptr(self._patch[i]) for i in range(3))
+        self._adv_err = ctypes.c_uint32(0)
         self.fast_steps = 0      # decode steps served by the device-side path (tests, profiling)
         self.staged_steps = 0
 
@@ -265,12 +266,22 @@ class RunnerGlue:
         st = self._fast
         if st is None or st["ids"] != ids_key or device_tokens is None:
             return None
+        # a row the kernel had to park at an EARLIER step (no block behind its new token): one host memory read
+        self.lib.nvllm_advance_decode_state_poll_error(ctypes.byref(self._adv_err), 0)
+        if self._adv_err.value:
+            row = self._adv_err.value - 1
+            self.lib.nvllm_advance_decode_state_poll_error(ctypes.byref(self._adv_err), 1)
+            self._fast = None
+            raise _lib.NvllmError(f"device-side prepare_decode: row {row} had no block for its new token (a block-table "
+                                  f"patch was missing); that row's output of the affected step is zeros")
         bs, bsz = st["bs"], self.block_size
-        lens = st["lens"]
-        lens += 1
-        if len(seqs[0]) != lens[0] or len(seqs[-1]) != lens[-1]:      # not "one more token each": restage
+        # every row must have grown by exactly one token, else the device state is stale: restage.  All rows are
+        # compared (bs <= 512: a few microseconds), and before the host copy of the lengths is touched.
+        now = np.fromiter(map(len, seqs), dtype=np.int64, count=bs) if len(seqs) == bs else None
+        if now is None or not np.array_equal(now, st["lens"] + 1):
             self._fast = None
             return None
+        lens = st["lens"] = now
         opened = np.flatnonzero((lens - 1) % bsz == 0)                 # rows whose new token starts a block
         n_patch = int(opened.size)
         width = old_width = st["width"]
@@ -312,7 +323,7 @@ class RunnerGlue:
         bs = len(seqs)
         ids_key = None
         if self.device_state:
-            ids_key = tuple([s.seq_id for s in seqs]) if hasattr(seqs[0], "seq_id") else None
+            ids_key = tuple(map(seq_identity, seqs))
             if ids_key is not None and device_tokens is not None and self._fast is not None:
                 out = self._advance_on_device(seqs, ids_key, device_tokens)
                 if out is not None:
@@ -336,8 +347,8 @@ class RunnerGlue:
         # ring slot, so the common step rewrites nothing but ids / positions / lens / slots.
         # Sequence identity is part of it: a batch where one running sequence was swapped for another of equal length
         # and equal last block must not inherit the staged table (tests/test_runner_glue.py::test_decode_swap...).
-        sig = (rows, cols, bs, width, tuple(getattr(s, "seq_id", id(s)) for s in seqs), tuple(map(len, tables)),
-               tuple(last_blocks))
+        sig = (rows, cols, bs, width, ids_key if ids_key is not None else tuple(map(seq_identity, seqs)),
+               tuple(map(len, tables)), tuple(last_blocks))
         if self._slot_sig[slot_idx] != sig:
             self._slot_sig[slot_idx] = sig
             if gbs is not None:
@@ -376,13 +387,61 @@ class RunnerGlue:
         return self.decode_views(self.dev, gbs, self.max_blocks)
 
 
+def seq_identity(seq):
+    """A key that names the same running sequence at every step and on every tensor-parallel rank.
+
+    `Sequence.seq_id` where the object has one.  The reference does not pickle it (engine/sequence.py:77-90), so the
+    copies a worker rank unpickles each step have none unless `install_sequence_identity` patched the class; for those
+    the key is (prompt length, first block id) -- stable over the life of a sequence, and distinct between running
+    sequences except for two that share their first prefix-cache block AND have equal prompt lengths, which the
+    per-row length / last-block terms of the staging signature still tell apart.  Never `id(seq)`: workers get
+    fresh objects every step, so an address is neither stable nor unique over time.
+    """
+    sid = getattr(seq, "seq_id", None)
+    if sid is not None:
+        return sid
+    bt = seq.block_table
+    return ("anon", getattr(seq, "num_prompt_tokens", -1), bt[0] if bt else -1)
+
+
+def install_sequence_identity(sequence_cls) -> None:
+    """Make `seq_id` survive the rank-0 -> worker pickle (reference: engine/sequence.py:77-90 drops it, so on worker
+    ranks every decode step took the staged path and the step was gated by the slowest rank).  The id travels as one
+    tagged trailing element that the patched `__setstate__` strips before the reference's own code sees the state,
+    so the reference's five fields keep their positions; both ends of the pipe import the same patched class
+    (model_runner.py is imported by every rank process)."""
+    if getattr(sequence_cls, "_nvllm_identity", False):
+        return
+    get0, set0 = sequence_cls.__getstate__, sequence_cls.__setstate__
+
+    def __getstate__(self):
+        return (*get0(self), ("nvllm_seq_id", getattr(self, "seq_id", None)))
+
+    def __setstate__(self, state):
+        tail = state[-1] if len(state) else None
+        if isinstance(tail, tuple) and len(tail) == 2 and tail[0] == "nvllm_seq_id":
+            state = state[:-1]
+            if tail[1] is not None:
+                self.seq_id = tail[1]
+        set0(self, state)
+
+    sequence_cls.__getstate__ = __getstate__
+    sequence_cls.__setstate__ = __setstate__
+    sequence_cls._nvllm_identity = True
+
+
 # ---------------------------------------------------------------------- engine integration
-def install(model_runner_cls, set_context: Callable, get_context: Callable, reset_context: Callable) -> None:
+def install(model_runner_cls, set_context: Callable, get_context: Callable, reset_context: Callable,
+            sequence_cls=None) -> None:
     """Swap the glue methods of the host engine's ModelRunner for the cuda backend.
 
     Called from the reference-side binding: the original methods stay in place for
     every other backend; dispatch is on `hf_config.attn_backend == "cuda"` per instance.
+    `sequence_cls` (the engine's Sequence): its pickled state additionally carries `seq_id`, which the device-side
+    decode path needs on worker ranks (install_sequence_identity).
     """
+    if sequence_cls is not None:
+        install_sequence_identity(sequence_cls)
     orig = {name: getattr(model_runner_cls, name) for name in
             ("prepare_block_tables", "prepare_prefill", "prepare_decode", "run_model", "capture_cudagraph")}
 
@@ -457,6 +516,22 @@ def install(model_runner_cls, set_context: Callable, get_context: Callable, rese
         g.graph_bs = list(self.graph_bs)
         self.graph_vars = dict(outputs=outputs, staging=g.dev)
 
+    orig_exit = getattr(model_runner_cls, "exit", None)
+
+    def exit(self):
+        # NVLLM_GLUE_STATS_DIR: every rank leaves its decode-path counters behind (tests assert that worker ranks take
+        # the device-side path too; spawned workers skip atexit handlers, so this hangs on the engine's own exit call)
+        import json
+        import os
+        d = os.environ.get("NVLLM_GLUE_STATS_DIR")
+        g = getattr(self, "_nvllm_glue", None)
+        if d and g is not None:
+            with open(os.path.join(d, f"glue_rank{getattr(self, 'rank', 0)}.json"), "w") as f:
+                json.dump({"rank": getattr(self, "rank", 0), "fast_steps": g.fast_steps, "staged_steps": g.staged_steps}, f)
+        return orig_exit(self)
+
+    if orig_exit is not None:
+        model_runner_cls.exit = exit
     for name, fn in (("prepare_block_tables", prepare_block_tables), ("prepare_prefill", prepare_prefill),
                      ("prepare_decode", prepare_decode), ("run_model", run_model),
                      ("capture_cudagraph", capture_cudagraph)):

@@ -188,3 +188,53 @@ def test_live_reference_trace_on_device(lib, unmodified_reference):
         _check(ctx, ids, pos, want, step)
         toks = torch.tensor([(( step + 1) * 13 + i) % 10000 for i in range(len(seqs))], dtype=torch.int64, device="cuda")
     assert g.fast_steps == 519 and g.staged_steps == 1
+
+
+def test_missing_block_parks_the_row_and_reaches_the_host(lib):
+    """a new token that lands in a table column holding -1 (its patch never arrived) used to become a
+    negative slot and an out-of-range page.  The kernel now parks that row (slot -1, context length 0), writes
+    1 + row to a mapped host word, and leaves the other rows exactly as the reference computes them."""
+    import ctypes
+    dev = "cuda"
+    bs, width = 3, 2
+    lens = torch.tensor([10, BS, 300], dtype=torch.int32, device=dev)          # row 1's next token opens column 1
+    tab = torch.tensor([[7, -1], [8, -1], [9, 11]], dtype=torch.int32, device=dev)
+    ids = torch.zeros(bs, dtype=torch.int64, device=dev)
+    pos = torch.zeros(bs, dtype=torch.int64, device=dev)
+    slots = torch.zeros(bs, dtype=torch.int32, device=dev)
+    sampled = torch.tensor([101, 102, 103], dtype=torch.int64, device=dev)
+    err = ctypes.c_uint32(7)
+    assert lib.nvllm_advance_decode_state_poll_error(ctypes.byref(err), 1) == 0
+    empty = (ctypes.c_int32 * 1)()
+    rc = lib.nvllm_advance_decode_state(ids.data_ptr(), pos.data_ptr(), slots.data_ptr(), lens.data_ptr(), tab.data_ptr(),
+                                        width, sampled.data_ptr(), bs, BS, empty, empty, empty, 0, 0, 0,
+                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert ids.tolist() == [101, 102, 103] and pos.tolist() == [11, BS + 1, 301]
+    assert lens.tolist() == [11, 0, 301]                       # parked: the decode kernel reads nothing for row 1
+    assert slots.tolist() == [7 * BS + 10, -1, 11 * BS + 300 - BS]   # -1: store_kvcache skips it
+    assert lib.nvllm_advance_decode_state_poll_error(ctypes.byref(err), 0) == 0 and err.value == 1 + 1
+    assert lib.nvllm_advance_decode_state_poll_error(ctypes.byref(err), 1) == 0
+    assert lib.nvllm_advance_decode_state_poll_error(ctypes.byref(err), 0) == 0 and err.value == 0
+    # the glue reads the word before its next device-side step, raises, and re-stages from the host afterwards
+    from nano_vllm_learn_b200 import _lib
+    ctx = Ctx()
+    g = _glue(ctx)
+    free = list(range(500, 100, -1))
+    seqs = [Seq(n, [free.pop() for _ in range((n + BS - 1) // BS)]) for n in (10, 300)]
+    g.prepare_decode(seqs)
+    g.prepare_decode(seqs, _step(seqs, free, 1))
+    assert g.fast_steps == 1
+    lens.copy_(torch.tensor([10, BS, 300], dtype=torch.int32))                # some launch parks a row ...
+    rc = lib.nvllm_advance_decode_state(ids.data_ptr(), pos.data_ptr(), slots.data_ptr(), lens.data_ptr(), tab.data_ptr(),
+                                        width, sampled.data_ptr(), bs, BS, empty, empty, empty, 0, 0, 0,
+                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    toks = _step(seqs, free, 2)
+    with pytest.raises(_lib.NvllmError, match="no block for its new token"):  # ... and the next step says so
+        g.prepare_decode(seqs, toks)
+    ids2, pos2 = g.prepare_decode(seqs, toks)                                  # word cleared, state dropped: staged
+    assert g.fast_steps == 1
+    _check(ctx, ids2, pos2, gorc.prepare_decode_ref(seqs), 2)

@@ -29,3 +29,10 @@ def test_tp2_engine_tokens_identical_with_vocab_parallel_sampling(tmp_path):
     assert rec["vp"]["identical_to_nccl"] is True and rec["vp"]["sampler"].endswith("sampler_cuda")
     assert rec["emb"]["identical_to_nccl"] is True            # fused VocabParallelEmbedding (edit A9): a bit-exact copy
     assert len(rec["tokens"]["vp"]) == 6 and all(len(t) == 24 for t in rec["tokens"]["vp"])
+    # with vocabulary-parallel sampling every rank holds the sampled ids on its device, and with seq_id in the
+    # pickled Sequence state (runner_glue.install_sequence_identity) worker ranks recognise an unchanged batch: rank 1
+    # must advance decode steps on the device like rank 0, not re-stage each one from the host.
+    stats = {r["rank"]: r for r in rec["vp"]["glue_stats"]}
+    assert set(stats) == {0, 1}
+    assert stats[1]["fast_steps"] > 0 and stats[1]["fast_steps"] == stats[0]["fast_steps"], stats
+    assert stats[1]["staged_steps"] == stats[0]["staged_steps"], stats

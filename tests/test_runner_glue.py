@@ -317,3 +317,113 @@ def test_device_side_path_host_logic_on_cpu(lib, graphs):
             assert got.dtype == want[k].dtype and torch.equal(got, want[k]), (step, k)
     assert shim.calls == g.fast_steps and g.fast_steps + g.staged_steps == 400
     assert g.fast_steps >= 380 and 1 <= shim.max_patches_seen <= 16
+
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _reference_sequence_cls():
+    import importlib
+    import sys
+    for cand in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference"):
+        if os.path.isdir(os.path.join(cand, "nanovllm")):
+            if cand not in sys.path:
+                sys.path.insert(0, cand)
+            return importlib.import_module("nanovllm.engine.sequence")
+    return None
+
+
+def test_worker_rank_copies_keep_their_identity_and_take_the_device_path(lib):
+    """worker ranks unpickle fresh Sequence objects every step and the reference's __getstate__ drops
+    seq_id, so rank > 0 never took the device-side path.  With install_sequence_identity the id travels in the pickle;
+    driving the glue with a pickled copy of the batch per step (what ModelRunner.loop hands a worker) must advance on
+    the device at every step after the first, and publish the reference's tensors."""
+    import copy
+    import itertools
+    import pickle
+    from nano_vllm_learn_b200 import runner_glue as rg
+    mod = _reference_sequence_cls()
+    if mod is None:
+        pytest.skip("reference tree not on this machine")
+    Sequence = type("Sequence", (mod.Sequence,), {})       # patch a subclass: the imported reference class stays stock
+    Sequence.__module__ = __name__
+    globals()["Sequence"] = Sequence                        # picklable by reference from this module
+    try:
+        plain = pickle.loads(pickle.dumps(Sequence([1, 2, 3])))
+        assert not hasattr(plain, "seq_id")                 # the reference behaviour the patch is for
+        rg.install_sequence_identity(Sequence)
+        rg.install_sequence_identity(Sequence)              # idempotent
+        free = itertools.count(10)
+        seqs = []
+        for n in (250, 3, 511, 700, 256):
+            s = Sequence(list(range(n)))
+            s.block_table = [next(free) for _ in range((n + BS - 1) // BS)]
+            seqs.append(s)
+        for s in seqs:                                      # prompt state and decode state both round-trip
+            c = pickle.loads(pickle.dumps(s))
+            assert c.seq_id == s.seq_id and c.token_ids == s.token_ids and c.block_table == s.block_table
+            assert (c.num_tokens, c.num_prompt_tokens, c.num_cached_tokens) == (s.num_tokens, s.num_prompt_tokens, 0)
+        ctx = Ctx()
+        g = _glue(lib, ctx, max_num_seqs=16)
+        g.device_state = True
+        shim = g.lib = _KernelShim(g.lib)
+        toks = None
+        for step in range(300):
+            toks = []
+            for i, s in enumerate(seqs):
+                s.append_token((step * 31 + i) % 10000)
+                if s.num_tokens % BS == 1:
+                    s.block_table.append(next(free))
+                toks.append(s.last_token)
+            worker_seqs = pickle.loads(pickle.dumps(seqs))   # fresh objects, as on rank > 0
+            assert worker_seqs[0] is not seqs[0] and not hasattr(worker_seqs[0], "token_ids")
+            assert [rg.seq_identity(w) for w in worker_seqs] == [s.seq_id for s in seqs]
+            ids_t, pos_t = g.prepare_decode(worker_seqs, torch.tensor(toks, dtype=torch.int64))
+            want = gorc.prepare_decode_ref(seqs)
+            assert torch.equal(ids_t, want["input_ids"]) and torch.equal(pos_t, want["positions"]), step
+            for k in ("slot_mapping", "context_lens", "block_tables"):
+                assert torch.equal(getattr(ctx.args, k), want[k]), (step, k)
+        # staged: the first step, and the one where the longest row opens a 4th block (the eager table gets wider)
+        assert g.staged_steps == 2 and g.fast_steps == 298 == shim.calls
+        # objects without any id (stock reference pickles): a stable surrogate, never the object's address
+        anon = [copy.copy(s) for s in seqs]
+        for a in anon:
+            del a.seq_id
+        assert [rg.seq_identity(a) for a in anon] == [("anon", s.num_prompt_tokens, s.block_table[0]) for s in seqs]
+    finally:
+        globals().pop("Sequence", None)
+
+
+def test_device_path_restages_when_a_middle_row_did_not_grow_by_one(lib):
+    """only the first and last rows were checked for 'one more token each'."""
+    import itertools
+    ctx = Ctx()
+    g = _glue(lib, ctx, max_num_seqs=16)
+    g.device_state = True
+    g.lib = _KernelShim(g.lib)
+    free = itertools.count(100)
+    seqs = []
+    for i, n in enumerate((250, 300, 40)):
+        s = Seq([1], [next(free) for _ in range((n + BS - 1) // BS)], 0, n, 1)
+        s.seq_id = i
+        seqs.append(s)
+    g.prepare_decode(seqs, None)
+    for s in seqs:
+        s.num_tokens += 1
+    g.prepare_decode(seqs, torch.tensor([1, 2, 3]))
+    assert (g.fast_steps, g.staged_steps) == (1, 1)
+    seqs[0].num_tokens += 1
+    seqs[1].num_tokens += 2                                  # the middle row jumps by two
+    seqs[2].num_tokens += 1
+    g.prepare_decode(seqs, torch.tensor([4, 5, 6]))
+    assert (g.fast_steps, g.staged_steps) == (1, 2)          # restaged from the host ...
+    want = gorc.prepare_decode_ref(seqs)
+    for k in ("slot_mapping", "context_lens", "block_tables"):
+        assert torch.equal(getattr(ctx.args, k), want[k]), k
+    for s in seqs:
+        s.num_tokens += 1
+    g.prepare_decode(seqs, torch.tensor([7, 8, 9]))
+    assert (g.fast_steps, g.staged_steps) == (2, 2)          # ... and the device path resumes from the new state
+    want = gorc.prepare_decode_ref(seqs)
+    for k in ("slot_mapping", "context_lens", "block_tables"):
+        assert torch.equal(getattr(ctx.args, k), want[k]), k

@@ -39,6 +39,10 @@ def child(args):
     import torch
     from nanovllm import LLM, SamplingParams
     os.environ["NVLLM_PORT"] = str(args.port)
+    import glob
+    import tempfile
+    stats_dir = tempfile.mkdtemp(prefix="nvllm_glue_stats_")
+    os.environ["NVLLM_GLUE_STATS_DIR"] = stats_dir     # inherited by the spawned worker ranks
     g = torch.Generator().manual_seed(11)
     prompts = [torch.randint(0, 10000, (n,), generator=g).tolist() for n in (300, 17, 64, 129, 255, 5)][:args.bs]
     llm = LLM(ns.model_path, enforce_eager=False, max_model_len=1024, max_num_seqs=16, attn_backend="cuda",
@@ -55,6 +59,10 @@ def child(args):
                "sampler": type(llm.model_runner.sampler).__module__}
     finally:
         llm.exit()
+    time.sleep(0.5)
+    # decode-path counters of every rank (runner_glue's exit hook): device-side steps / host-staged steps
+    rec["glue_stats"] = sorted((json.load(open(p)) for p in glob.glob(os.path.join(stats_dir, "glue_rank*.json"))),
+                               key=lambda r: r["rank"])
     with open(args.child_out, "w") as f:
         json.dump(rec, f)
 

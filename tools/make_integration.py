@@ -35,7 +35,7 @@ EDITS = [
     ("nanovllm/engine/model_runner.py", None,
      '\n\n# --- cuda attention backend: B200-native prepare/capture glue (other backends keep the methods above)\n'
      'from nano_vllm_learn_b200.runner_glue import install as _install_cuda_glue\n'
-     '_install_cuda_glue(ModelRunner, set_context, get_context, reset_context)\n'),
+     '_install_cuda_glue(ModelRunner, set_context, get_context, reset_context, sequence_cls=Sequence)\n'),
     # ---- A5 (optional: NVLLM_FUSED_PRE_ATTN=0 keeps the reference's separate kernels):
     #      q/k RMSNorm + RoPE + store_kvcache fused into one launch before attention (nanovllm/models/qwen3.py:105-118)
     ("nanovllm/models/qwen3.py",
