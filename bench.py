@@ -400,16 +400,63 @@ def run_cuda(args):
             "cpu_baseline": cpu, "vs_flash": vs_flash, "tp_strong": tp_strong, "long_ctx": long_ctx,
             "prefill": prefill, "fused_allreduce": fused, "vocab_parallel_sampler": vp_sampler,
             "fused_embedding": fused_emb, "tp_e2e": tp_e2e}
+    # The line is ~25 KB and a log that keeps only its tail loses the legs printed first (missing #3): the
+    # LAST key repeats, in under 1.5 KB, the one or two numbers of every leg that the claims in DESIGN.md rest on.
+    line["digest"] = leg_digest(line)
     print(json.dumps(line), flush=True)
 
 
+def leg_digest(line):
+    """Compact copy of the comparator / scaling / parity numbers of every leg (values only, no prose)."""
+    def pick(d, *keys):
+        return {k: d[k] for k in keys if isinstance(d, dict) and k in d} if isinstance(d, dict) else None
+    out = {"roofline_frac": (line.get("roofline") or {}).get("frac"),
+           "e2e": (line.get("e2e") or {}).get("value")}
+    out["vs_flash"] = pick(line.get("vs_flash"), "decode_us", "flash_attn_decode_us", "speedup", "max_abs_diff")
+    out["tp_strong"] = pick(line.get("tp_strong"), "us_per_launch_max_over_ranks", "per_gpu_GBps", "frac_of_measured_peak")
+    if isinstance(line.get("long_ctx"), list):
+        out["long_ctx"] = [[r.get("bs"), r.get("heads", "")[:8], r.get("graph_us_per_launch"), r.get("GBps"),
+                            r.get("flash_attn_graph_us_per_launch")] for r in line["long_ctx"] if isinstance(r, dict)]
+    if isinstance(line.get("prefill"), list):
+        out["prefill"] = [[r.get("us"), r.get("achieved"), r.get("frac"), r.get("flash_attn_us")]
+                          for r in line["prefill"] if isinstance(r, dict)]
+    for leg in ("fused_allreduce", "vocab_parallel_sampler", "fused_embedding"):
+        v = line.get(leg)
+        if isinstance(v, dict):
+            rows = v.get("rows") or v.get("shapes") or []
+            out[leg] = {"parity_ok": v.get("parity_ok"),
+                        "speedup_min_max": [min((r.get("speedup", 0) for r in rows if isinstance(r, dict)), default=None),
+                                            max((r.get("speedup", 0) for r in rows if isinstance(r, dict)), default=None)]}
+    e = line.get("tp_e2e")
+    if isinstance(e, dict):
+        out["tp_e2e"] = {"arms": {a.get("arm"): a.get("tok_s") for a in e.get("arms", []) if isinstance(a, dict)},
+                         "cuda_over_flash": e.get("cuda_over_flash")}
+    return out
+
+
+def decode_kernel_digest():
+    """sha256 over the sources the decode kernel is compiled from; profiles/decode_traffic.json records it."""
+    import hashlib
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "nano-vllm-learn_b200", "csrc")
+    for name in ("common.cuh", "paged_decode.cu", "paged_decode_params.cuh"):
+        with open(os.path.join(csrc, name), "rb") as f:
+            h.update(name.encode())
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def load_traffic():
-    """dram bytes per launch of the decode kernel from the committed ncu summary, if present."""
+    """dram bytes per launch of the decode kernel from the committed ncu summary -- None when the summary was taken on
+    other kernel sources than the ones in this tree (tools/make_decode_traffic.py writes the digest)."""
     path = os.path.join(ROOT, "profiles", "decode_traffic.json")
     if os.path.exists(path):
         try:
             with open(path) as f:
-                return json.load(f).get("dram_bytes_per_launch")
+                rec = json.load(f)
+            if rec.get("kernel_source_sha256") != decode_kernel_digest():
+                return None
+            return rec.get("dram_bytes_per_launch")
         except Exception:
             return None
     return None
